@@ -1,0 +1,160 @@
+/*
+ * mpcb.h -- C ABI of the B200 batched minimum-time Panda OCP solver (libmpcb.so).
+ *
+ * This is the drop-in boundary for the reference's hot path: everything MotionPlanner::solve_trajectory does
+ * behind `mpc.solve()` (/root/reference/mpc_solver/motionPlanner.cpp:177-208) -- polympc's SQP + boxADMM over
+ * minTime_ocp (mpc_solver/robot_ocp.hpp) with MySolver's regularisation and line search
+ * (mpc_solver/polympc_redef.hpp) and pinocchio's RNEA -- for a BATCH of independent start->target problems.
+ * Plain C types only (no torch, no Eigen); every call returns 0 on success and a negative mpcb_error otherwise.
+ * There is no CPU fallback: without a CUDA device mpcb_create fails with MPCB_ERR_NO_DEVICE.
+ *
+ * Variable layout of one OCP (polympc's; motionPlanner.cpp:162-165, motionPlanner.hpp:159-162), N = PO*NS+1 nodes:
+ *     z      = [ x_0 .. x_{N-1} (14 each: q(7), v(7)) | u_0 .. u_{N-1} (7 each) | p ]        index 0 <-> t = 0
+ *     lambda = [ eq (14*(N-1)) | ineq (8*N) | box (21*N+1, same order as z) ]
+ * Batch arrays are problem-major and contiguous (problem i at offset i*stride).
+ */
+#ifndef MPCB_H
+#define MPCB_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    MPCB_OK = 0,
+    MPCB_ERR_NO_DEVICE = -1,     /* no CUDA device / driver: the product has no CPU path */
+    MPCB_ERR_BAD_ARG = -2,
+    MPCB_ERR_UNSUPPORTED = -3,   /* (poly_order, num_seg) not instantiated, or an option the kernels do not implement */
+    MPCB_ERR_CUDA = -4,          /* a CUDA runtime call failed; see mpcb_last_error() */
+    MPCB_ERR_ALLOC = -5
+} mpcb_error;
+
+/* Solver settings.  Defaults = what MotionPlanner's constructor sets (motionPlanner.cpp:15-20) on top of
+ * polympc's defaults. */
+typedef struct {
+    int poly_order;               /* robot_ocp.hpp:31  POLY_ORDER (3) */
+    int num_seg;                  /* robot_ocp.hpp:32  NUM_SEG (6) */
+    int sqp_max_iter;             /* motionPlanner.cpp:15 (2) */
+    int qp_max_iter;              /* motionPlanner.cpp:16 (700) */
+    int line_search_max_iter;     /* motionPlanner.cpp:17 (10 -> at most 9 trials, polympc_redef.hpp:101) */
+    int qp_check_termination;     /* boxADMM: residual test every 25 iterations */
+    int qp_adaptive_rho;          /* boxADMM adaptive rho (0 = off; 1 is MPCB_ERR_UNSUPPORTED in this version) */
+    int qp_adaptive_rho_interval;
+    double qp_eps_abs;            /* motionPlanner.cpp:20 (1e-3) */
+    double qp_eps_rel;            /* motionPlanner.cpp:19 (1e-3) */
+    double qp_rho;                /* 0.1 */
+    double qp_sigma;              /* 1e-6 */
+    double qp_alpha;              /* 1.0 */
+    double qp_adaptive_rho_tolerance;
+    double sqp_eps_prim;          /* 1e-3 */
+    double sqp_eps_dual;          /* 1e-3 */
+    double sqp_tau;               /* line-search contraction 0.5 */
+    double sqp_eta;               /* Armijo constant 0.25 */
+    double hess_reg;              /* polympc_redef.hpp:68 (0.001) */
+} mpcb_settings;
+
+/* Robot limits (robot_utils/pandaWrapper.hpp:29-40) and the planner's margins / tolerances
+ * (motionPlanner.cpp:56-100, motionPlanner.hpp:44). */
+typedef struct {
+    double qmin[7], qmax[7], vmax[7], amax[7], taumax[7], jmax[7];
+    double margins[5];            /* position, velocity, acceleration, torque, jerk */
+    double min_height;            /* tool height lower bound */
+    double final_eps;             /* final state box half-width (1e-2) */
+    double p_lb, p_ub;            /* bounds on the final time (0, 10) */
+} mpcb_limits;
+
+/* Per-problem solver report (polympc's sqp info + the quantities the termination test uses). */
+typedef struct {
+    int status;                   /* 1 = SOLVED, 2 = MAX_ITER_EXCEEDED */
+    int sqp_iters;
+    int qp_iters_total;
+    int qp_status[4];             /* per SQP iteration (first 4): 1 = solved, 2 = max iter */
+    int qp_iters[4];
+    double alpha[4];              /* accepted (or last) line-search step */
+    int ls_trials[4];
+    double primal_step_norm, dual_step_norm, max_violation, l1_violation, cost;
+} mpcb_stats;
+
+/* Per-trajectory accounting of examples/benchmark.cpp:118-194 (MPC half). */
+typedef struct {
+    int flags[4];                 /* jerk, linear velocity, angular velocity, collision; 1 = ok */
+    double mins[28], maxs[28];    /* q, v, a, tau extrema over the samples */
+    double final_err[14];         /* last sample - target */
+} mpcb_account;
+
+typedef struct mpcb_handle mpcb_handle;
+
+enum { MPCB_MEM_HOST = 0, MPCB_MEM_DEVICE = 1 };
+
+void mpcb_default_settings(mpcb_settings* s);
+void mpcb_default_limits(mpcb_limits* l);            /* Panda limits, margins 1 (motionPlanner.cpp:24) */
+
+/* Sizes for a (poly_order, num_seg) pair. */
+int mpcb_num_nodes(const mpcb_settings* s);
+int mpcb_num_var(const mpcb_settings* s);
+int mpcb_num_dual(const mpcb_settings* s);
+/* Normalised node times in [0,1], ascending (polympc `time_nodes`; motionPlanner.cpp:156). */
+int mpcb_time_nodes(const mpcb_settings* s, double* t /*N*/);
+
+/* One handle per CUDA device; not thread-safe; replaces the `mpc_t mpc` member (motionPlanner.hpp:28-29). */
+int mpcb_create(const mpcb_settings* s, int device, mpcb_handle** out);
+void mpcb_destroy(mpcb_handle* h);
+const char* mpcb_last_error(const mpcb_handle* h);   /* h may be NULL: error of the last failed mpcb_create */
+
+/* Replaces set_constraint_margins / set_min_height / the limits table (motionPlanner.cpp:56-100). */
+int mpcb_set_limits(mpcb_handle* h, const mpcb_limits* lim);
+
+/*
+ * Solve n independent OCPs (replaces n calls of mpc.solve(), motionPlanner.cpp:184, with the bounds
+ * set_current_state / set_target_state would install, motionPlanner.cpp:27-54).
+ *   x0, xT      n x 14       initial state (pinned) and target state (box +- final_eps)
+ *   guess_x     n x 14N      initial guess at the nodes (what warm_start_RK writes, motionPlanner.cpp:156-174)
+ *   guess_u     n x 7N
+ *   guess_T     n
+ *   guess_lam   n x ndual or NULL (zeros)
+ *   sol_x/sol_u/sol_T          outputs, same layouts;  sol_lam  n x ndual or NULL;  stats  n or NULL
+ *   mem         MPCB_MEM_HOST: plain host pointers, copies are made inside the call (synchronous);
+ *               MPCB_MEM_DEVICE: device pointers on the handle's device, the call only enqueues work on `stream`
+ *   stream      cudaStream_t (NULL = default stream)
+ */
+int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, const double* guess_x,
+                     const double* guess_u, const double* guess_T, const double* guess_lam, double* sol_x,
+                     double* sol_u, double* sol_T, double* sol_lam, mpcb_stats* stats, int mem, void* stream);
+
+/*
+ * Read-out + accounting (get_MPC_trajectory<npts>, motionPlanner.hpp:99-116; benchmark.cpp:118-194):
+ *   traj   n x (npts+1) x 29  rows [t, q(7), v(7), a(7), tau(7)]  (may be NULL)
+ *   acc    n                  (may be NULL);   target n x 14 (needed when acc != NULL)
+ */
+int mpcb_sample_batch(mpcb_handle* h, int n, const double* sol_x, const double* sol_u, const double* sol_T,
+                      const double* target, int npts, double* traj, mpcb_account* acc, int mem, void* stream);
+
+/* Device time of the last mpcb_solve_batch kernel on this handle, in milliseconds (CUDA events on the launch
+ * stream); < 0 if none.  Synchronises the stream. */
+double mpcb_last_solve_ms(mpcb_handle* h);
+/* Number of kernel launches issued by this handle so far. */
+long long mpcb_launch_count(const mpcb_handle* h);
+
+/* FP64 FMA peak micro-benchmark on the handle's device (roofline denominator); returns TFLOP/s. */
+double mpcb_measure_fp64_tflops(mpcb_handle* h);
+
+/* ---- host-side helpers of the planner (no GPU work) ------------------------------------------------------ */
+
+/* MotionPlanner::sample_random_state (motionPlanner.cpp:102-114) + the benchmark's target generation
+ * (examples/benchmark.cpp:19-42), with a counter-based RNG instead of std::rand.
+ *   kind 0: mpc_benchmark -- start fixed at mid-range at rest, random target pose, target velocity from a random
+ *           Cartesian tool velocity through the damped pseudo-inverse, with the benchmark's scale-downs
+ *   kind 1: offline_trajectory -- random start and target states (examples/offline_trajectory.cpp:18-41)
+ * Outputs x0, xT: n x 14. */
+int mpcb_generate_problems(const mpcb_limits* lim, int kind, unsigned long long seed, int n, double* x0, double* xT);
+
+/* Initial guess at the collocation nodes (stand-in for warm_start_RK, motionPlanner.cpp:146-175: Ruckig is not
+ * available): time-scaled cubic Hermite joint profile whose duration is the smallest one on a
+ * geometric grid that respects the velocity and acceleration margins. */
+int mpcb_guess_batch(const mpcb_settings* s, const mpcb_limits* lim, int n, const double* x0, const double* xT,
+                     double* guess_x, double* guess_u, double* guess_T);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,24 @@
+# Builds libmpcb.so (the C-ABI product library: CUDA kernels for sm_100a + host planner code), in-tree.
+NVCC ?= nvcc
+CXX ?= g++
+CUDA_HOME ?= /usr/local/cuda
+SRC = mpc_motion_planner_b200/csrc
+OUT = mpc_motion_planner_b200/libmpcb.so
+NVFLAGS = -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Iinclude -I$(SRC) -Xcompiler -fPIC
+CXXFLAGS = -O2 -std=c++17 -fPIC -Wall -Iinclude -I$(SRC) -I$(CUDA_HOME)/include
+HDR = $(wildcard $(SRC)/*.h) include/mpcb.h
+
+all: $(OUT)
+build/mpcb_kernels.o: $(SRC)/mpcb_kernels.cu $(HDR)
+	@mkdir -p build
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+build/mpcb_capi.o: $(SRC)/mpcb_capi.cpp $(HDR)
+	@mkdir -p build
+	$(CXX) $(CXXFLAGS) -c $< -o $@
+build/mpcb_planner_host.o: $(SRC)/mpcb_planner_host.cpp $(HDR)
+	@mkdir -p build
+	$(CXX) $(CXXFLAGS) -c $< -o $@
+$(OUT): build/mpcb_kernels.o build/mpcb_capi.o build/mpcb_planner_host.o
+	$(NVCC) -shared -o $@ $^ -cudart shared -Xlinker -rpath=$(CUDA_HOME)/lib64
+clean:
+	rm -rf build $(OUT)

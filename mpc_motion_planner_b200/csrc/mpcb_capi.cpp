@@ -1,0 +1,258 @@
+// Implementation of the C ABI (include/mpcb.h): handle management, host<->device staging, kernel launches.
+// There is deliberately no CPU path: every compute entry point needs a CUDA device.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <string>
+
+#include "mpcb.h"
+#include "mpcb_host_util.h"
+#include "mpcb_kernels.h"
+
+using namespace mpcb;
+
+struct mpcb_handle {
+    int device = 0;
+    int sm_count = 0;
+    mpcb_settings st;
+    mpcb_limits lim;
+    KernelConst kc;
+    int grid_max = 0;
+    int* d_counter = nullptr;
+    double* d_workspace = nullptr;
+    // staging buffers for MPCB_MEM_HOST calls (grown on demand)
+    void* d_stage = nullptr;
+    size_t stage_bytes = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    cudaStream_t timed_stream = nullptr;
+    long long launches = 0;
+    std::string err;
+};
+
+static std::string g_create_error;
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                           \
+            return MPCB_ERR_CUDA;                                                                  \
+        }                                                                                          \
+    } while (0)
+
+static void refresh_const(mpcb_handle* h) {
+    h->kc.st = h->st;
+    mpcb_fill_cheb(h->st.poly_order, h->st.num_seg, &h->kc.cheb);
+    fill_limtab(&h->lim, h->kc.limtab);
+    for (int j = 0; j < 7; j++) h->kc.jmax[j] = h->lim.jmax[j];
+}
+
+extern "C" {
+
+int mpcb_create(const mpcb_settings* s, int device, mpcb_handle** out) {
+    if (!s || !out) { g_create_error = "null argument"; return MPCB_ERR_BAD_ARG; }
+    *out = nullptr;
+    const char* why = "";
+    if (!settings_supported(s, &why)) { g_create_error = why; return MPCB_ERR_UNSUPPORTED; }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_create_error = std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0") +
+                         " (libmpcb has no CPU path)";
+        return MPCB_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= ndev) { g_create_error = "device index out of range"; return MPCB_ERR_BAD_ARG; }
+    mpcb_handle* h = new mpcb_handle();
+    h->device = device; h->st = *s;
+    default_limits(&h->lim);
+    refresh_const(h);
+    auto fail = [&](const char* what, cudaError_t ce) {
+        g_create_error = std::string(what) + ": " + cudaGetErrorString(ce);
+        mpcb_destroy(h);
+        return (int)MPCB_ERR_CUDA;
+    };
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("cudaSetDevice", e);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
+    h->sm_count = prop.multiProcessorCount;
+    if ((size_t)prop.sharedMemPerBlockOptin < solve_smem_bytes()) {
+        g_create_error = "device offers too little opt-in shared memory per block for the OCP kernel";
+        mpcb_destroy(h);
+        return MPCB_ERR_UNSUPPORTED;
+    }
+    if ((e = solve_prepare()) != cudaSuccess) return fail("cudaFuncSetAttribute(solve_kernel)", e);
+    h->grid_max = h->sm_count;      // one CTA per SM (shared memory bound)
+    if ((e = cudaMalloc(&h->d_counter, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaMalloc(&h->d_workspace, sizeof(double) * solve_workspace_doubles_per_cta() * h->grid_max)) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+    *out = h;
+    return MPCB_OK;
+}
+
+void mpcb_destroy(mpcb_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->d_counter) cudaFree(h->d_counter);
+    if (h->d_workspace) cudaFree(h->d_workspace);
+    if (h->d_stage) cudaFree(h->d_stage);
+    if (h->ev0) cudaEventDestroy(h->ev0);
+    if (h->ev1) cudaEventDestroy(h->ev1);
+    delete h;
+}
+
+const char* mpcb_last_error(const mpcb_handle* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int mpcb_set_limits(mpcb_handle* h, const mpcb_limits* lim) {
+    if (!h || !lim) return MPCB_ERR_BAD_ARG;
+    h->lim = *lim;
+    refresh_const(h);
+    return MPCB_OK;
+}
+
+static int ensure_stage(mpcb_handle* h, size_t bytes) {
+    if (bytes <= h->stage_bytes) return MPCB_OK;
+    if (h->d_stage) { cudaFree(h->d_stage); h->d_stage = nullptr; h->stage_bytes = 0; }
+    cudaError_t e = cudaMalloc(&h->d_stage, bytes);
+    if (e != cudaSuccess) { h->err = std::string("cudaMalloc(stage): ") + cudaGetErrorString(e); return MPCB_ERR_ALLOC; }
+    h->stage_bytes = bytes;
+    return MPCB_OK;
+}
+static size_t al(size_t b) { return (b + 255) / 256 * 256; }
+
+int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, const double* guess_x, const double* guess_u,
+                     const double* guess_T, const double* guess_lam, double* sol_x, double* sol_u, double* sol_T, double* sol_lam,
+                     mpcb_stats* stats, int mem, void* stream_) {
+    if (!h) return MPCB_ERR_BAD_ARG;
+    if (n < 0 || (n > 0 && (!x0 || !xT || !guess_x || !guess_u || !guess_T || !sol_x || !sol_u || !sol_T))) { h->err = "null or negative argument"; return MPCB_ERR_BAD_ARG; }
+    if (mem != MPCB_MEM_HOST && mem != MPCB_MEM_DEVICE) { h->err = "mem must be MPCB_MEM_HOST or MPCB_MEM_DEVICE"; return MPCB_ERR_BAD_ARG; }
+    if (n == 0) return MPCB_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CK(cudaSetDevice(h->device));
+    const int N = mpcb_num_nodes(&h->st), ND = mpcb_num_dual(&h->st);
+    const size_t bx0 = sizeof(double) * 14 * n, bgx = sizeof(double) * 14 * N * n, bgu = sizeof(double) * 7 * N * n, bT = sizeof(double) * n,
+                 blam = sizeof(double) * ND * n, bst = sizeof(mpcb_stats) * n;
+    BatchPtrs bp;
+    memset(&bp, 0, sizeof bp);
+    if (mem == MPCB_MEM_DEVICE) {
+        bp.x0 = x0; bp.xT = xT; bp.gx = guess_x; bp.gu = guess_u; bp.gT = guess_T; bp.glam = guess_lam;
+        bp.sx = sol_x; bp.su = sol_u; bp.sT = sol_T; bp.slam = sol_lam; bp.stats = stats;
+    } else {
+        const size_t total = 2 * al(bx0) + 2 * al(bgx) + 2 * al(bgu) + 2 * al(bT) + (guess_lam ? al(blam) : 0) + (sol_lam ? al(blam) : 0) + (stats ? al(bst) : 0);
+        int rc = ensure_stage(h, total);
+        if (rc) return rc;
+        char* p = (char*)h->d_stage;
+        auto take = [&](size_t b) { char* r = p; p += al(b); return r; };
+        double* dx0 = (double*)take(bx0); double* dxT = (double*)take(bx0);
+        double* dgx = (double*)take(bgx); double* dgu = (double*)take(bgu); double* dgT = (double*)take(bT);
+        double* dsx = (double*)take(bgx); double* dsu = (double*)take(bgu); double* dsT = (double*)take(bT);
+        double* dgl = guess_lam ? (double*)take(blam) : nullptr;
+        double* dsl = sol_lam ? (double*)take(blam) : nullptr;
+        mpcb_stats* dst = stats ? (mpcb_stats*)take(bst) : nullptr;
+        CK(cudaMemcpyAsync(dx0, x0, bx0, cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(dxT, xT, bx0, cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(dgx, guess_x, bgx, cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(dgu, guess_u, bgu, cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(dgT, guess_T, bT, cudaMemcpyHostToDevice, stream));
+        if (dgl) CK(cudaMemcpyAsync(dgl, guess_lam, blam, cudaMemcpyHostToDevice, stream));
+        bp.x0 = dx0; bp.xT = dxT; bp.gx = dgx; bp.gu = dgu; bp.gT = dgT; bp.glam = dgl;
+        bp.sx = dsx; bp.su = dsu; bp.sT = dsT; bp.slam = dsl; bp.stats = dst;
+    }
+    const int grid = n < h->grid_max ? n : h->grid_max;
+    CK(cudaEventRecord(h->ev0, stream));
+    CK(launch_solve(h->kc, bp, n, grid, h->d_counter, h->d_workspace, stream));
+    CK(cudaEventRecord(h->ev1, stream));
+    h->launches += 1;
+    h->timed = true; h->timed_stream = stream;
+    if (mem == MPCB_MEM_HOST) {
+        CK(cudaMemcpyAsync(sol_x, bp.sx, bgx, cudaMemcpyDeviceToHost, stream));
+        CK(cudaMemcpyAsync(sol_u, bp.su, bgu, cudaMemcpyDeviceToHost, stream));
+        CK(cudaMemcpyAsync(sol_T, bp.sT, bT, cudaMemcpyDeviceToHost, stream));
+        if (sol_lam) CK(cudaMemcpyAsync(sol_lam, bp.slam, blam, cudaMemcpyDeviceToHost, stream));
+        if (stats) CK(cudaMemcpyAsync(stats, bp.stats, bst, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+    }
+    return MPCB_OK;
+}
+
+int mpcb_sample_batch(mpcb_handle* h, int n, const double* sol_x, const double* sol_u, const double* sol_T, const double* target,
+                      int npts, double* traj, mpcb_account* acc, int mem, void* stream_) {
+    if (!h) return MPCB_ERR_BAD_ARG;
+    if (n < 0 || npts < 1 || npts > 1000 || (n > 0 && (!sol_x || !sol_u || !sol_T)) || (acc && !target)) { h->err = "bad argument"; return MPCB_ERR_BAD_ARG; }
+    if (mem != MPCB_MEM_HOST && mem != MPCB_MEM_DEVICE) { h->err = "mem must be MPCB_MEM_HOST or MPCB_MEM_DEVICE"; return MPCB_ERR_BAD_ARG; }
+    if (n == 0 || (!traj && !acc)) return MPCB_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CK(cudaSetDevice(h->device));
+    const int N = mpcb_num_nodes(&h->st);
+    const size_t bsx = sizeof(double) * 14 * N * n, bsu = sizeof(double) * 7 * N * n, bT = sizeof(double) * n, btg = sizeof(double) * 14 * n,
+                 btraj = sizeof(double) * 29 * (npts + 1) * n, bacc = sizeof(mpcb_account) * n;
+    const double *dsx = sol_x, *dsu = sol_u, *dsT = sol_T, *dtg = target;
+    double* dtraj = traj;
+    mpcb_account* dacc = acc;
+    if (mem == MPCB_MEM_HOST) {
+        const size_t total = al(bsx) + al(bsu) + al(bT) + (acc ? al(btg) + al(bacc) : 0) + (traj ? al(btraj) : 0);
+        int rc = ensure_stage(h, total);
+        if (rc) return rc;
+        char* p = (char*)h->d_stage;
+        auto take = [&](size_t b) { char* r = p; p += al(b); return r; };
+        double* a = (double*)take(bsx); double* b = (double*)take(bsu); double* c = (double*)take(bT);
+        CK(cudaMemcpyAsync(a, sol_x, bsx, cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(b, sol_u, bsu, cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(c, sol_T, bT, cudaMemcpyHostToDevice, stream));
+        dsx = a; dsu = b; dsT = c;
+        if (acc) {
+            double* t = (double*)take(btg);
+            CK(cudaMemcpyAsync(t, target, btg, cudaMemcpyHostToDevice, stream));
+            dtg = t; dacc = (mpcb_account*)take(bacc);
+        }
+        if (traj) dtraj = (double*)take(btraj);
+    }
+    const int grid = n < 8 * h->sm_count ? n : 8 * h->sm_count;
+    CK(launch_sample(h->kc, dsx, dsu, dsT, dtg, npts, dtraj, dacc, n, grid, stream));
+    h->launches += 1;
+    if (mem == MPCB_MEM_HOST) {
+        if (traj) CK(cudaMemcpyAsync(traj, dtraj, btraj, cudaMemcpyDeviceToHost, stream));
+        if (acc) CK(cudaMemcpyAsync(acc, dacc, bacc, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+    }
+    return MPCB_OK;
+}
+
+double mpcb_last_solve_ms(mpcb_handle* h) {
+    if (!h || !h->timed) return -1.0;
+    cudaSetDevice(h->device);
+    if (cudaEventSynchronize(h->ev1) != cudaSuccess) return -1.0;
+    float ms = -1.f;
+    if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) return -1.0;
+    return (double)ms;
+}
+long long mpcb_launch_count(const mpcb_handle* h) { return h ? h->launches : 0; }
+
+double mpcb_measure_fp64_tflops(mpcb_handle* h) {
+    if (!h) return -1.0;
+    cudaSetDevice(h->device);
+    const int blocks = h->sm_count * 8, threads = 256, iters = 1 << 16;
+    double* out = nullptr;
+    if (cudaMalloc(&out, sizeof(double) * blocks * threads) != cudaSuccess) return -1.0;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    double best = 0;
+    for (int rep = 0; rep < 4; rep++) {
+        cudaEventRecord(a, 0);
+        launch_fp64_peak(out, blocks, threads, iters, 0);
+        cudaEventRecord(b, 0);
+        if (cudaEventSynchronize(b) != cudaSuccess) { best = -1.0; break; }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, a, b);
+        h->launches += 1;
+        const double fl = 2.0 * 8.0 * (double)iters * blocks * threads;
+        const double tf = fl / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(out);
+    return best;
+}
+
+}  // extern "C"

@@ -1,0 +1,222 @@
+// Per-CTA context, per-thread persistent state and the lockstep-phase machinery of the OCP kernel.
+//
+// One CTA (NT threads) solves one OCP at a time.  The solver is written as a sequence of PHASES: inside a phase every
+// thread works on its own items and never reads what another thread writes in the same phase; phases are separated by
+// a CTA barrier.  The same source compiles in two modes:
+//   * nvcc (default): __device__ code, a phase is `stmt; __syncthreads();`                      <- the product
+//   * -DMPCB_EMUL (g++ only, tests/emul): a phase is a loop over all thread ids on the host     <- test-only lockstep
+//     emulation used by the CPU test-suite to check the kernel's index logic without a GPU.  It is never linked into
+//     libmpcb.so; the product has no CPU path.
+#pragma once
+#include <string.h>
+#include "mpcb.h"
+#include "mpcb_common.h"
+#include "mpcb_rbd.h"
+#include "mpcb_shape.h"
+
+namespace mpcb {
+
+constexpr int NT = 512;   // threads per CTA
+
+#ifdef MPCB_EMUL
+#define MPCB_DEV inline
+#define MPCB_DRIVER_PARAMS(SH) Ctx<SH>& c, TS<SH>* tsv
+#define MPCB_DRIVER_ARGS c, tsv
+#define MPCB_PHASE(...)                       \
+    for (int tid = 0; tid < NT; ++tid) {      \
+        TS<SH>& ts = tsv[tid];                \
+        (void)ts;                             \
+        __VA_ARGS__;                          \
+    }
+#else
+#define MPCB_DEV __device__ __forceinline__
+#define MPCB_DRIVER_PARAMS(SH) Ctx<SH>& c, TS<SH>& ts, const int tid
+#define MPCB_DRIVER_ARGS c, ts, tid
+#define MPCB_PHASE(...)  \
+    {                    \
+        __VA_ARGS__;     \
+        __syncthreads(); \
+    }
+#endif
+
+// uniform double scalars in shared memory
+enum {
+    SC_PBAR = 0,   // p at the linearisation point
+    SC_MTP,        // -ts * pbar
+    SC_HDP,        // regularised H[p,p]
+    SC_RHSP,       // rhs[p] gather part
+    SC_MU, SC_V_L1, SC_V_LINF, SC_PHI0, SC_DPHI, SC_ALPHA, SC_COST_TRIAL, SC_PN, SC_DN, SC_GRADP,
+    SC_RP, SC_RD, SC_EP, SC_ED,
+    SC_COUNT = 24
+};
+// uniform int scalars
+enum { IS_QP_DONE = 0, IS_QP_STATUS, IS_QP_ITERS, IS_LS_ACCEPT, IS_SQP_DONE, IS_COUNT = 8 };
+// atomic-max slots
+enum { UM_RP = 0, UM_RD, UM_NAX, UM_NX, UM_NZ, UM_NHX, UM_NATY, UM_NH, UM_A, UM_B, UM_V, UM_COUNT = 12 };
+
+template <class SH>
+struct Layout {   // offsets in doubles into the dynamic shared-memory block
+    static constexpr int MAT = 0;                                  // W | F | C   (also: derivative scratch, QP result)
+    static constexpr int W = MAT, F = W + SH::WSIZE, C = F + SH::FSIZE;
+    static constexpr int BB = MAT + SH::MATSIZE;
+    static constexpr int JG = BB + SH::BBSIZE;
+    static constexpr int VW = JG + SH::NN * 8 * 22;                // w      (rows)
+    static constexpr int VRHS = VW + SH::VP;                       // rhs    (vars; rows in the residual check)
+    static constexpr int VXT = VRHS + SH::VP;                      // x~     (vars)
+    static constexpr int HA = VXT + SH::VP;                        // Hessian arrow (vars, kernel order)
+    static constexpr int PCOL = HA + SH::VP;                       // A[:, p] of the equality rows
+    static constexpr int PART = PCOL + SH::NEQ;                    // F^T rhs partials
+    static constexpr int PSUM = PART + SH::PARTSIZE + 1;           // 2 x 32 partial sums
+    static constexpr int COLBUF = PSUM + 64;                       // NS pivot columns
+    static constexpr int COLSTRIDE = (SH::AUGMAX + 7) / 8 * 8;
+    static constexpr int LIMS = COLBUF + (SH::NS > 1 ? SH::NS : 1) * COLSTRIDE;   // per-joint bounds 5x7 + 5, x0, xT
+    static constexpr int SCAL = LIMS + 72;
+    static constexpr int UMAX = SCAL + SC_COUNT;
+    static constexpr int ISC = UMAX + UM_COUNT;
+    static constexpr int TOTAL = ISC + IS_COUNT;                   // ints stored in 8-byte slots for simplicity
+    static constexpr size_t BYTES = (size_t)TOTAL * 8;
+    static constexpr int DERIV_STRIDE = (int)(sizeof(rbd::DerivScratch) / 8) + 1;
+    static_assert(SH::NN * DERIV_STRIDE <= SH::MATSIZE + SH::BBSIZE, "derivative scratch must fit the matrix area");
+    static_assert(SH::NDUAL + SH::VP <= SH::MATSIZE, "QP result must fit the matrix area");
+};
+// LIMS sub-offsets
+enum { LM_QLO = 0, LM_QHI = 7, LM_V = 14, LM_A = 21, LM_TAU = 28, LM_MINH = 35, LM_EPS, LM_PLB, LM_PUB, LM_X0 = 40, LM_XT = 54 };
+
+template <class SH>
+struct Ctx {
+    double* sm;                    // shared-memory block
+    double *W, *F, *C, *BB, *Jg, *w, *rhs, *xt, *Ha, *pcol, *part, *psum, *colbuf, *lims, *scal;
+    unsigned long long* umax;
+    long long* isc;
+    double* z;                     // global workspace: iterate, kernel order (NVAR)
+    double* lam;                   // global workspace: multipliers [eq | ineq | box kernel order]
+    const mpcb_settings* st;
+    const ChebConst* cheb;
+    // results of the last QP, aliased onto the matrix area after the ADMM loop
+    double* qp_p;                  // step p, kernel order
+    double* qp_lam;                // QP multipliers
+    MPCB_HD void bind(double* smem) {
+        typedef Layout<SH> L;
+        sm = smem;
+        W = sm + L::W; F = sm + L::F; C = sm + L::C; BB = sm + L::BB; Jg = sm + L::JG; w = sm + L::VW; rhs = sm + L::VRHS;
+        xt = sm + L::VXT; Ha = sm + L::HA; pcol = sm + L::PCOL; part = sm + L::PART; psum = sm + L::PSUM;
+        colbuf = sm + L::COLBUF; lims = sm + L::LIMS; scal = sm + L::SCAL;
+        umax = reinterpret_cast<unsigned long long*>(sm + L::UMAX);
+        isc = reinterpret_cast<long long*>(sm + L::ISC);
+        qp_p = sm + L::MAT; qp_lam = sm + L::MAT + SH::VP;
+    }
+};
+
+// Per-thread persistent state ("registers" on the device).
+template <class SH>
+struct TS {
+    // ---- row role: thread r < NA owns constraint row r
+    double l, u, rho, zA, yA, pc;
+    double dco[SH::PO + 1];
+    int ridx[SH::PO + 2];
+    // ---- variable role: thread i < NVAR owns variable i (kernel order)
+    double x, zB, yB, lb, ub, rhoB, ha, hd;
+    double gco[2 * SH::PO];
+    int grow[2 * SH::PO];
+    int gn, gfrow, gk, gcol;
+    int vk, vcomp, vseg, vloc;
+};
+
+// ---- small helpers ------------------------------------------------------------------------------------------------
+MPCB_DEV void umax_accum(unsigned long long* slot, double v) {
+#ifdef MPCB_EMUL
+    unsigned long long b;
+    memcpy(&b, &v, 8);
+    if (b > *slot) *slot = b;
+#else
+    unsigned long long b = (unsigned long long)__double_as_longlong(v);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        unsigned long long t = __shfl_xor_sync(0xffffffffu, b, o);
+        b = (t > b) ? t : b;
+    }
+    if ((threadIdx.x & 31) == 0) atomicMax(slot, b);
+#endif
+}
+MPCB_DEV double umax_get(const unsigned long long* slot) {
+    double v;
+    unsigned long long b = *slot;
+    memcpy(&v, &b, 8);
+    return v;
+}
+MPCB_DEV double dmax(double a, double b) { return a > b ? a : b; }
+MPCB_DEV double dmin(double a, double b) { return a < b ? a : b; }
+
+// Box bounds of variable (k, comp) -- MotionPlanner::set_constraint_margins / set_current_state / set_target_state
+// (/root/reference/mpc_solver/motionPlanner.cpp:27-54,64-80).  Pins are always applied last.
+template <class SH>
+MPCB_DEV void var_bounds(const Ctx<SH>& c, int k, int comp, double& lo, double& hi) {
+    const double* L = c.lims;
+    if (k < 0) { lo = L[LM_PLB]; hi = L[LM_PUB]; return; }
+    if (comp < 14 && k == 0) { lo = hi = L[LM_X0 + comp]; return; }
+    if (comp < 14 && k == SH::NN - 1) { lo = L[LM_XT + comp] - L[LM_EPS]; hi = L[LM_XT + comp] + L[LM_EPS]; return; }
+    if (comp < 7) { lo = L[LM_QLO + comp]; hi = L[LM_QHI + comp]; return; }
+    if (comp < 14) { hi = L[LM_V + comp - 7]; lo = -hi; return; }
+    hi = L[LM_A + comp - 14]; lo = -hi;
+}
+// Bounds of inequality output rr (0-6 torque, 7 tool height) -- motionPlanner.cpp:82-97
+template <class SH>
+MPCB_DEV void ineq_bounds(const Ctx<SH>& c, int rr, double& lo, double& hi) {
+    if (rr < 7) { hi = c.lims[LM_TAU + rr]; lo = -hi; }
+    else { lo = c.lims[LM_MINH]; hi = INFINITY; }
+}
+// boxADMM's per-row penalty: loose rows 1e-6, equality rows 1e3*rho, else rho
+MPCB_DEV double row_rho(double lo, double hi, double rho) {
+    if (lo < -1e16 && hi > 1e16) return 1e-6;
+    return (fabs(hi - lo) < 1e-4) ? 1e3 * rho : rho;
+}
+
+// Static (problem-independent) part of the per-thread roles.  All TS arrays are indexed with compile-time constants
+// after unrolling so that the struct stays in registers.
+template <class SH>
+MPCB_DEV void setup_roles(const Ctx<SH>& c, TS<SH>& ts, int tid) {
+    const ChebConst& cb = *c.cheb;
+    MPCB_UNROLL
+    for (int l = 0; l < SH::PO + 2; l++) ts.ridx[l] = 0;
+    MPCB_UNROLL
+    for (int l = 0; l <= SH::PO; l++) ts.dco[l] = 0;
+    if (tid < SH::NEQ) {
+        const int k = tid / 14, cc = tid % 14, s = k / SH::PO, j = k - s * SH::PO;
+        MPCB_UNROLL
+        for (int l = 0; l <= SH::PO; l++) { ts.ridx[l] = SH::kvar(s * SH::PO + l, cc); ts.dco[l] = cb.D[j][l]; }
+        ts.ridx[SH::PO + 1] = (cc < 7) ? SH::kvar(k, 7 + cc) : SH::kvar(k, 14 + (cc - 7));
+    } else if (tid < SH::NA) {
+        const int k = (tid - SH::NEQ) / 8;
+        ts.ridx[0] = SH::kvar(k, 0);
+        ts.ridx[1] = SH::kvar(k, 14);
+    }
+    ts.gn = 0; ts.gfrow = -1; ts.gk = -1; ts.gcol = 0; ts.vk = -1; ts.vcomp = 0; ts.vseg = -1; ts.vloc = 0;
+    MPCB_UNROLL
+    for (int n = 0; n < 2 * SH::PO; n++) { ts.grow[n] = 0; ts.gco[n] = 0; }
+    ts.l = ts.u = ts.rho = ts.zA = ts.yA = ts.pc = 0;
+    ts.x = ts.zB = ts.yB = ts.lb = ts.ub = ts.rhoB = ts.ha = ts.hd = 0;
+    if (tid < SH::NVAR) {
+        int k, comp, seg, loc;
+        SH::decode(tid, k, comp, seg, loc);
+        ts.vk = k; ts.vcomp = comp; ts.vseg = seg; ts.vloc = loc;
+        if (k >= 0) {
+            ts.gk = k; ts.gcol = comp;
+            if (comp < 14) {
+                // collocation rows containing x_{k,comp}: rows of segment s1 (k is its local node l1) in slots [0,PO),
+                // and, for a junction, rows of segment s1-1 (k is its end node) in slots [PO,2PO)
+                const int s1 = k / SH::PO, l1 = k - s1 * SH::PO;
+                const bool own = k < SH::NN - 1, prev = (l1 == 0 && k > 0);
+                MPCB_UNROLL
+                for (int j = 0; j < SH::PO; j++) {
+                    if (own) { ts.grow[j] = 14 * (s1 * SH::PO + j) + comp; ts.gco[j] = cb.D[j][l1]; }
+                    if (prev) { ts.grow[SH::PO + j] = 14 * ((s1 - 1) * SH::PO + j) + comp; ts.gco[SH::PO + j] = cb.D[j][SH::PO]; }
+                }
+                if (comp >= 7 && k < SH::NN - 1) ts.gfrow = 14 * k + (comp - 7);
+            } else if (k < SH::NN - 1) {
+                ts.gfrow = 14 * k + 7 + (comp - 14);
+            }
+        }
+    }
+}
+
+}  // namespace mpcb

@@ -1,0 +1,170 @@
+// CUDA kernels (sm_100a) of the batched OCP solver and their launchers.
+//   solve_kernel   : persistent CTAs, one OCP per CTA at a time; the whole SQP (linearise, factorise, <=700 ADMM
+//                    iterations, line search) runs out of shared memory -- phases in mpcb_qp.h / mpcb_admm.h / mpcb_sqp.h
+//   sample_kernel  : read-out + benchmark accounting (get_MPC_trajectory<N>, /root/reference/mpc_solver/motionPlanner.hpp:99-116;
+//                    examples/benchmark.cpp:118-194)
+//   fp64_peak_kernel: FP64 FMA throughput micro-benchmark (roofline denominator)
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "mpcb_kernels.h"
+#include "mpcb_sqp.h"
+
+namespace mpcb {
+
+template <class SH>
+__global__ void __launch_bounds__(NT, 1)
+solve_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, const int n, int* __restrict__ counter, double* __restrict__ workspace) {
+    extern __shared__ double smem[];
+    __shared__ int s_next;
+    const int tid = threadIdx.x;
+    Ctx<SH> c;
+    c.bind(smem);
+    c.z = workspace + (size_t)blockIdx.x * (SH::VP + SH::NDUAL + 8);
+    c.lam = c.z + SH::VP;
+    c.st = &kc.st;
+    c.cheb = &kc.cheb;
+    TS<SH> ts;
+    setup_roles(c, ts, tid);
+    for (;;) {
+        if (tid == 0) s_next = atomicAdd(counter, 1);
+        __syncthreads();
+        const int i = s_next;
+        __syncthreads();
+        if (i >= n) break;
+        Problem pb;
+        pb.limtab = kc.limtab;
+        pb.x0 = bp.x0 + (size_t)14 * i; pb.xT = bp.xT + (size_t)14 * i;
+        pb.gx = bp.gx + (size_t)14 * SH::NN * i; pb.gu = bp.gu + (size_t)7 * SH::NN * i;
+        pb.glam = bp.glam ? bp.glam + (size_t)SH::NDUAL * i : nullptr;
+        pb.gT = bp.gT[i];
+        pb.sx = bp.sx + (size_t)14 * SH::NN * i; pb.su = bp.su + (size_t)7 * SH::NN * i; pb.sT = bp.sT + i;
+        pb.slam = bp.slam ? bp.slam + (size_t)SH::NDUAL * i : nullptr;
+        pb.stats = bp.stats ? bp.stats + i : nullptr;
+        solve_ocp<SH>(c, ts, tid, pb);
+    }
+}
+
+// ---- read-out + accounting ------------------------------------------------------------------------------------------
+constexpr int SAMPLE_NT = 256;
+
+template <class SH>
+__global__ void __launch_bounds__(SAMPLE_NT)
+sample_kernel(const __grid_constant__ KernelConst kc, const double* __restrict__ sol_x, const double* __restrict__ sol_u,
+              const double* __restrict__ sol_T, const double* __restrict__ target, const int npts, double* __restrict__ traj,
+              mpcb_account* __restrict__ acc, const int n) {
+    extern __shared__ double rows[];            // (npts+1) x 29
+    __shared__ int flags[4];
+    const int tid = threadIdx.x;
+    for (int ocp = blockIdx.x; ocp < n; ocp += gridDim.x) {
+        const double* sx = sol_x + (size_t)14 * SH::NN * ocp;
+        const double* su = sol_u + (size_t)7 * SH::NN * ocp;
+        const double T = sol_T[ocp];
+        if (tid < 4) flags[tid] = 1;
+        __syncthreads();
+        for (int i = tid; i <= npts; i += SAMPLE_NT) {
+            // polympc solution_x_at / solution_u_at: Lagrange interpolation on the segment containing t
+            double t = 1.0 / npts * i;                      // motionPlanner.hpp:103
+            double* row = rows + 29 * i;
+            double tc = fmin(fmax(t, 0.0), 1.0);
+            int s = (int)floor(tc * SH::NS);
+            if (s > SH::NS - 1) s = SH::NS - 1;
+            const double xi = 2.0 * (tc * SH::NS - s) - 1.0;
+            double wgt[SH::PO + 1];
+#pragma unroll
+            for (int j = 0; j <= SH::PO; j++) {
+                double num = 1, den = 1;
+#pragma unroll
+                for (int l = 0; l <= SH::PO; l++)
+                    if (l != j) { num *= (xi - kc.cheb.xi[l]); den *= (kc.cheb.xi[j] - kc.cheb.xi[l]); }
+                wgt[j] = num / den;
+            }
+            for (int cc = 0; cc < 21; cc++) row[1 + cc] = 0;
+#pragma unroll
+            for (int j = 0; j <= SH::PO; j++) {
+                const int k = s * SH::PO + j;
+                for (int cc = 0; cc < 7; cc++) {
+                    row[1 + cc] += wgt[j] * sx[14 * k + cc];
+                    row[8 + cc] += wgt[j] * sx[14 * k + 7 + cc];
+                    row[15 + cc] += wgt[j] * su[7 * k + cc];
+                }
+            }
+            double q[7], v[7], a[7], g[8];
+            for (int cc = 0; cc < 7; cc++) { q[cc] = row[1 + cc]; v[cc] = row[8 + cc]; a[cc] = row[15 + cc]; }
+            rbd::node_constraints_value(q, v, a, g);        // torque by RNEA (motionPlanner.hpp:110-113)
+            for (int cc = 0; cc < 7; cc++) row[22 + cc] = g[cc];
+            row[0] = t * T;                                 // motionPlanner.hpp:115
+            if (acc) {
+                // benchmark.cpp:140-156: Cartesian velocity limits and collision with the ground
+                double oR[7][9], op[7][3], J[42], pos[3], tv[6];
+                rbd::fk_world(q, oR, op);
+                rbd::frame_jacobian(oR, op, PANDA(PANDA_TOOL_OFFSET), J, pos);
+                for (int r = 0; r < 6; r++) { double sum = 0; for (int j = 0; j < 7; j++) sum += J[r * 7 + j] * v[j]; tv[r] = sum; }
+                if (sqrt(tv[0] * tv[0] + tv[1] * tv[1] + tv[2] * tv[2]) > 1.7) flags[1] = 0;
+                if (sqrt(tv[3] * tv[3] + tv[4] * tv[4] + tv[5] * tv[5]) > 2.5) flags[2] = 0;
+                if (pos[2] < 0) flags[3] = 0;
+            }
+        }
+        __syncthreads();
+        if (acc) {
+            const double dT = rows[29 * npts] / npts;       // benchmark.cpp:128
+            for (int i = 1 + tid; i <= npts; i += SAMPLE_NT)
+                for (int j = 0; j < 7; j++) {
+                    const double jerk = (rows[29 * i + 15 + j] - rows[29 * (i - 1) + 15 + j]) / dT;
+                    if (fabs(jerk) > 10 * kc.jmax[j]) flags[0] = 0;      // benchmark.cpp:135
+                }
+            if (tid < 28) {
+                double mn = INFINITY, mx = -INFINITY;
+                for (int i = 0; i <= npts; i++) { const double x = rows[29 * i + 1 + tid]; mn = fmin(mn, x); mx = fmax(mx, x); }
+                acc[ocp].mins[tid] = mn; acc[ocp].maxs[tid] = mx;
+            }
+            if (tid < 14) acc[ocp].final_err[tid] = rows[29 * npts + 1 + tid] - target[(size_t)14 * ocp + tid];
+        }
+        if (traj)
+            for (int e = tid; e < 29 * (npts + 1); e += SAMPLE_NT) traj[(size_t)ocp * 29 * (npts + 1) + e] = rows[e];
+        __syncthreads();
+        if (acc && tid < 4) acc[ocp].flags[tid] = flags[tid];
+        __syncthreads();
+    }
+}
+
+// ---- FP64 FMA peak ---------------------------------------------------------------------------------------------------
+__global__ void fp64_peak_kernel(double* out, int iters) {
+    double a0 = threadIdx.x * 1e-3, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double b = 0.999999, cc = 1e-7;
+    for (int i = 0; i < iters; i++) {
+        a0 = fma(a0, b, cc); a1 = fma(a1, b, cc); a2 = fma(a2, b, cc); a3 = fma(a3, b, cc);
+        a4 = fma(a4, b, cc); a5 = fma(a5, b, cc); a6 = fma(a6, b, cc); a7 = fma(a7, b, cc);
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+// ---- launchers -------------------------------------------------------------------------------------------------------
+typedef Shape<3, 6> SH36;
+
+size_t solve_smem_bytes() { return Layout<SH36>::BYTES; }
+size_t solve_workspace_doubles_per_cta() { return SH36::VP + SH36::NDUAL + 8; }
+
+cudaError_t solve_prepare() {
+    return cudaFuncSetAttribute(solve_kernel<SH36>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Layout<SH36>::BYTES);
+}
+cudaError_t launch_solve(const KernelConst& kc, const BatchPtrs& bp, int n, int grid, int* counter, double* workspace, cudaStream_t stream) {
+    cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
+    if (e != cudaSuccess) return e;
+    solve_kernel<SH36><<<grid, NT, Layout<SH36>::BYTES, stream>>>(kc, bp, n, counter, workspace);
+    return cudaGetLastError();
+}
+cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double* su, const double* sT, const double* target, int npts,
+                          double* traj, mpcb_account* acc, int n, int grid, cudaStream_t stream) {
+    const size_t smem = (size_t)29 * (npts + 1) * sizeof(double);
+    cudaError_t e = cudaFuncSetAttribute(sample_kernel<SH36>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    sample_kernel<SH36><<<grid, SAMPLE_NT, smem, stream>>>(kc, sx, su, sT, target, npts, traj, acc, n);
+    return cudaGetLastError();
+}
+cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream) {
+    fp64_peak_kernel<<<blocks, threads, 0, stream>>>(out, iters);
+    return cudaGetLastError();
+}
+
+}  // namespace mpcb

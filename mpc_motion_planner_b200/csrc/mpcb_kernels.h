@@ -1,0 +1,32 @@
+// Interface between the C-ABI implementation (mpcb_capi.cpp, host C++) and the CUDA translation unit (mpcb_kernels.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include "mpcb.h"
+#include "mpcb_shape.h"
+
+namespace mpcb {
+
+// Launch-invariant constants, passed as a __grid_constant__ kernel parameter.
+struct KernelConst {
+    mpcb_settings st;
+    ChebConst cheb;
+    double limtab[40];      // fill_limtab()
+    double jmax[7];         // for the jerk flag of the accounting kernel
+};
+// Device pointers of one batch (problem-major arrays, layouts in mpcb.h).
+struct BatchPtrs {
+    const double *x0, *xT, *gx, *gu, *gT, *glam;
+    double *sx, *su, *sT, *slam;
+    mpcb_stats* stats;
+};
+
+size_t solve_smem_bytes();
+size_t solve_workspace_doubles_per_cta();
+cudaError_t solve_prepare();
+cudaError_t launch_solve(const KernelConst& kc, const BatchPtrs& bp, int n, int grid, int* counter, double* workspace, cudaStream_t stream);
+cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double* su, const double* sT, const double* target, int npts,
+                          double* traj, mpcb_account* acc, int n, int grid, cudaStream_t stream);
+cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream);
+
+}  // namespace mpcb

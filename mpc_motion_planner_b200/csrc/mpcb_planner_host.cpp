@@ -1,0 +1,202 @@
+// Host-side planner helpers behind the C ABI: problem generation and the initial guess (no GPU work).
+//
+//   mpcb_generate_problems : MotionPlanner::sample_random_state (/root/reference/mpc_solver/motionPlanner.cpp:102-114)
+//                            + the target generation of examples/benchmark.cpp:19-42 (kind 0) and
+//                            examples/offline_trajectory.cpp:18-41 (kind 1), using PandaWrapper::inverse_velocities /
+//                            forward_velocities (robot_utils/pandaWrapper.cpp:60-107).
+//   mpcb_guess_batch       : stand-in for MotionPlanner::warm_start_RK (motionPlanner.cpp:146-175).  Ruckig is not
+//                            available in this environment, so the guess is a time-scaled cubic
+//                            Hermite joint profile sampled at polympc's node times; see DESIGN.md.
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#include "mpcb.h"
+#include "mpcb_host_util.h"
+#include "mpcb_rbd.h"
+#include "mpcb_shape.h"
+
+namespace {
+
+using namespace mpcb;
+
+// counter-based RNG: splitmix64 of (seed, stream, counter) -> U(-1,1)   (replaces Eigen::Random / std::rand, Q13)
+struct Rng {
+    uint64_t state;
+    Rng(uint64_t seed, uint64_t stream) : state(seed * 0x9E3779B97F4A7C15ull + stream * 0xD1B54A32D192ED03ull + 0x632BE59BD9B4E019ull) {}
+    uint64_t next() {
+        uint64_t z = (state += 0x9E3779B97F4A7C15ull);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    }
+    double sym() { return 2.0 * ((next() >> 11) * (1.0 / 9007199254740992.0)) - 1.0; }
+};
+
+const double MAX_LINEAR_VELOCITY = 1.7, MAX_ANGULAR_VELOCITY = 2.5;   // pandaWrapper.hpp:37-38
+
+// world-aligned tool Jacobian (6x7)
+void tool_jacobian(const double* q, double* J) {
+    double oR[7][9], op[7][3];
+    rbd::fk_world(q, oR, op);
+    rbd::frame_jacobian(oR, op, PANDA(PANDA_TOOL_OFFSET), J, nullptr);
+}
+void forward_velocities(const double* q, const double* qd, double* tv) {    // pandaWrapper.cpp:90-107
+    double J[42];
+    tool_jacobian(q, J);
+    for (int r = 0; r < 6; r++) { double s = 0; for (int j = 0; j < 7; j++) s += J[r * 7 + j] * qd[j]; tv[r] = s; }
+}
+// J^T (J J^T + 1e-5 I)^-1 v   with an LDL^T solve of the 6x6 system                  // pandaWrapper.cpp:60-88
+void inverse_velocities(const double* q, const double* task, double* qd) {
+    double J[42], A[36], L[36], D[6], y[6];
+    tool_jacobian(q, J);
+    for (int r = 0; r < 6; r++)
+        for (int c = 0; c < 6; c++) { double s = 0; for (int j = 0; j < 7; j++) s += J[r * 7 + j] * J[c * 7 + j]; A[r * 6 + c] = s + (r == c ? 1e-5 : 0.0); }
+    memset(L, 0, sizeof L);
+    for (int j = 0; j < 6; j++) {
+        double d = A[j * 6 + j];
+        for (int k = 0; k < j; k++) d -= L[j * 6 + k] * L[j * 6 + k] * D[k];
+        D[j] = d; L[j * 6 + j] = 1;
+        for (int i = j + 1; i < 6; i++) {
+            double s = A[i * 6 + j];
+            for (int k = 0; k < j; k++) s -= L[i * 6 + k] * L[j * 6 + k] * D[k];
+            L[i * 6 + j] = s / d;
+        }
+    }
+    for (int i = 0; i < 6; i++) { double s = task[i]; for (int k = 0; k < i; k++) s -= L[i * 6 + k] * y[k]; y[i] = s; }
+    for (int i = 0; i < 6; i++) y[i] /= D[i];
+    for (int i = 5; i >= 0; i--) { double s = y[i]; for (int k = i + 1; k < 6; k++) s -= L[k * 6 + i] * y[k]; y[i] = s; }
+    for (int j = 0; j < 7; j++) { double s = 0; for (int r = 0; r < 6; r++) s += J[r * 7 + j] * y[r]; qd[j] = s; }
+}
+double norm3(const double* v) { return sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); }
+
+// sample_random_state (motionPlanner.cpp:102-114): rejection on the height of JOINT 7 (not the tool, Q12)
+void sample_random_state(const mpcb_limits* lim, Rng& rng, double* q, double* v) {
+    const double mp = lim->margins[0], mv = lim->margins[1];
+    const double zero[3] = {0, 0, 0};
+    double pos[3];
+    do {
+        for (int j = 0; j < 7; j++) {
+            const double range = lim->qmax[j] - lim->qmin[j];
+            const double safety = (1 - mp) * range / 2;
+            q[j] = 0.5 * (rng.sym() * (range - 2 * safety) + (lim->qmax[j] + lim->qmin[j]));
+        }
+        rbd::fk_point7(q, zero, pos);
+    } while (pos[2] < lim->min_height);
+    for (int j = 0; j < 7; j++) v[j] = mv * rng.sym() * lim->vmax[j];
+}
+// Cartesian scale-downs shared by both examples (benchmark.cpp:25-36, offline_trajectory.cpp:26-39)
+void scale_task_velocity(const double* q, double* v) {
+    double tv[6];
+    forward_velocities(q, v, tv);
+    if (norm3(tv) > MAX_LINEAR_VELOCITY) {
+        const double f = 0.9 * MAX_LINEAR_VELOCITY / norm3(tv);
+        for (int j = 0; j < 7; j++) v[j] *= f;
+        forward_velocities(q, v, tv);
+    }
+    if (norm3(tv + 3) > MAX_ANGULAR_VELOCITY) {
+        const double f = 0.9 * MAX_ANGULAR_VELOCITY / norm3(tv + 3);
+        for (int j = 0; j < 7; j++) v[j] *= f;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int mpcb_generate_problems(const mpcb_limits* lim, int kind, unsigned long long seed, int n, double* x0, double* xT) {
+    if (!lim || !x0 || !xT || n < 0 || (kind != 0 && kind != 1)) return MPCB_ERR_BAD_ARG;
+    for (int i = 0; i < n; i++) {
+        Rng rng(seed, (uint64_t)i);
+        double* a = x0 + 14 * (size_t)i;
+        double* b = xT + 14 * (size_t)i;
+        if (kind == 0) {
+            // start: mid-range pose at rest (MotionPlanner constructor, motionPlanner.cpp:5-8; never reset in benchmark.cpp)
+            for (int j = 0; j < 7; j++) { a[j] = (lim->qmax[j] + lim->qmin[j]) / 2; a[7 + j] = 0; }
+            sample_random_state(lim, rng, b, b + 7);
+            double task[6] = {rng.sym() * MAX_LINEAR_VELOCITY, rng.sym() * MAX_LINEAR_VELOCITY, rng.sym() * MAX_LINEAR_VELOCITY, 0, 0, 0};
+            inverse_velocities(b, task, b + 7);                                     // benchmark.cpp:20
+            scale_task_velocity(b, b + 7);                                          // benchmark.cpp:22-36
+            double worst = 0;                                                       // benchmark.cpp:38-42
+            bool any = false;
+            for (int j = 0; j < 7; j++) {
+                const double r = fabs(b[7 + j]) / (lim->margins[1] * lim->vmax[j]);
+                if (r > 1) any = true;
+                if (r > worst) worst = r;
+            }
+            if (any) for (int j = 0; j < 7; j++) b[7 + j] /= 1.1 * worst;
+        } else {
+            sample_random_state(lim, rng, a, a + 7);                                // offline_trajectory.cpp:18-19
+            sample_random_state(lim, rng, b, b + 7);                                // :22
+            scale_task_velocity(b, b + 7);                                          // :26-39
+        }
+    }
+    return MPCB_OK;
+}
+
+int mpcb_num_nodes(const mpcb_settings* s) { return s->poly_order * s->num_seg + 1; }
+int mpcb_num_var(const mpcb_settings* s) { return 21 * mpcb_num_nodes(s) + 1; }
+int mpcb_num_dual(const mpcb_settings* s) { const int n = mpcb_num_nodes(s); return 14 * (n - 1) + 8 * n + 21 * n + 1; }
+int mpcb_time_nodes(const mpcb_settings* s, double* t) {
+    if (!s || !t || s->poly_order < 1 || s->poly_order > 7 || s->num_seg < 1) return MPCB_ERR_BAD_ARG;
+    ChebConst cc;
+    mpcb_fill_cheb(s->poly_order, s->num_seg, &cc);
+    for (int sg = 0; sg < s->num_seg; sg++)
+        for (int j = 0; j <= s->poly_order; j++) t[sg * s->poly_order + j] = ((double)sg + 0.5 * (1.0 + cc.xi[j])) / s->num_seg;
+    return MPCB_OK;
+}
+void mpcb_default_settings(mpcb_settings* s) { default_settings(s); }
+void mpcb_default_limits(mpcb_limits* l) { default_limits(l); }
+
+// Cubic Hermite joint profile q(s), s = t/T, between (q0, v0) and (q1, v1); T = first value of the geometric grid
+// T_j = 0.05 * 1.05^j (capped at p_ub) for which |v| <= m_v v_max over [0,T] and |a| <= m_a a_max (the acceleration is
+// linear in s, so its extrema are at the ends; the velocity is quadratic, extrema at the ends or at the vertex).
+int mpcb_guess_batch(const mpcb_settings* s, const mpcb_limits* lim, int n, const double* x0, const double* xT, double* gx,
+                     double* gu, double* gT) {
+    if (!s || !lim || !x0 || !xT || !gx || !gu || !gT || n < 0) return MPCB_ERR_BAD_ARG;
+    const int N = mpcb_num_nodes(s);
+    if (N > 128) return MPCB_ERR_BAD_ARG;
+    double tn[128];
+    if (mpcb_time_nodes(s, tn) != MPCB_OK) return MPCB_ERR_BAD_ARG;
+    for (int i = 0; i < n; i++) {
+        const double *q0 = x0 + 14 * (size_t)i, *v0 = q0 + 7, *q1 = xT + 14 * (size_t)i, *v1 = q1 + 7;
+        double T = 0.05;
+        for (;;) {
+            bool ok = true;
+            for (int j = 0; j < 7 && ok; j++) {
+                const double dq = q1[j] - q0[j], vl = lim->margins[1] * lim->vmax[j], al = lim->margins[2] * lim->amax[j];
+                const double a0 = (6 * dq / T - 4 * v0[j] - 2 * v1[j]) / T, a1 = (-6 * dq / T + 2 * v0[j] + 4 * v1[j]) / T;
+                if (fabs(a0) > al || fabs(a1) > al) { ok = false; break; }
+                // v(s) = v0 + a0 T s + (a1 - a0) T s^2 / 2 ; vertex at s* = -a0 / (a1 - a0)
+                if (a1 != a0) {
+                    const double sv = -a0 / (a1 - a0);
+                    if (sv > 0 && sv < 1) {
+                        const double vv = v0[j] + a0 * T * sv + 0.5 * (a1 - a0) * T * sv * sv;
+                        if (fabs(vv) > vl) ok = false;
+                    }
+                }
+            }
+            if (ok || T >= lim->p_ub) break;
+            T *= 1.05;
+            if (T > lim->p_ub) T = lim->p_ub;
+        }
+        gT[i] = T;
+        for (int k = 0; k < N; k++) {
+            const double sg = tn[k];
+            const double h00 = 2 * sg * sg * sg - 3 * sg * sg + 1, h10 = sg * sg * sg - 2 * sg * sg + sg, h01 = -2 * sg * sg * sg + 3 * sg * sg,
+                         h11 = sg * sg * sg - sg * sg;
+            const double d00 = 6 * sg * sg - 6 * sg, d10 = 3 * sg * sg - 4 * sg + 1, d01 = -6 * sg * sg + 6 * sg, d11 = 3 * sg * sg - 2 * sg;
+            const double e00 = 12 * sg - 6, e10 = 6 * sg - 4, e01 = -12 * sg + 6, e11 = 6 * sg - 2;
+            double* xk = gx + ((size_t)i * N + k) * 14;
+            double* uk = gu + ((size_t)i * N + k) * 7;
+            for (int j = 0; j < 7; j++) {
+                xk[j] = h00 * q0[j] + h10 * T * v0[j] + h01 * q1[j] + h11 * T * v1[j];
+                xk[7 + j] = (d00 * q0[j] + d10 * T * v0[j] + d01 * q1[j] + d11 * T * v1[j]) / T;
+                uk[j] = (e00 * q0[j] + e10 * T * v0[j] + e01 * q1[j] + e11 * T * v1[j]) / (T * T);
+            }
+        }
+    }
+    return MPCB_OK;
+}
+
+}  // extern "C"

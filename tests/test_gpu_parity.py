@@ -1,0 +1,127 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (libmpcb.so), against the CPU oracle on the same seeded
+inputs.  Tolerances are north_star's: identical status classification, final time within 1e-6 relative, trajectories
+within 1e-5 absolute per collocation node, identical violation accounting."""
+import numpy as np
+import pytest
+
+import mpc_motion_planner_b200 as M
+
+pytestmark = pytest.mark.gpu
+
+BENCH_MARGINS = [0.8, 0.8, 0.6, 0.9, 0.1]      # examples/benchmark.cpp:9
+OFFLINE_MARGINS = [0.9, 0.9, 0.5, 0.9, 0.1]    # examples/offline_trajectory.cpp:9
+
+
+def _problems(kind, seed, n, margins):
+    lim = M.default_limits(margins)
+    s = M.default_settings()
+    x0, xT = M.generate_problems(lim, kind, seed, n)
+    gx, gu, gT = M.guess_batch(s, lim, x0, xT)
+    return s, lim, x0, xT, gx, gu, gT
+
+
+def _stats_tuple(st):
+    return (int(st["status"]), int(st["sqp_iters"]), list(st["qp_iters"]), list(st["qp_status"]), list(st["ls_trials"]), list(st["alpha"]))
+
+
+def _ostats_tuple(st):
+    return (st.status, st.sqp_iters, list(st.qp_iters), list(st.qp_status), list(st.ls_trials), list(st.alpha))
+
+
+@pytest.fixture(scope="module")
+def solver():
+    sv = M.Solver(M.default_settings(), M.default_limits(BENCH_MARGINS))
+    yield sv
+    sv.close()
+
+
+@pytest.mark.parametrize("kind,seed,margins,n", [(0, 1, BENCH_MARGINS, 24), (1, 0, OFFLINE_MARGINS, 12)])
+def test_solve_matches_oracle(oracle, solver, kind, seed, margins, n):
+    s, lim, x0, xT, gx, gu, gT = _problems(kind, seed, n, margins)
+    solver.set_limits(lim)
+    sx, su, sT, slam, st = solver.solve(x0, xT, gx, gu, gT, want_lam=True)
+    so = oracle.default_settings(); lo = oracle.default_limits(margins)
+    osx, osu, oT, ost = oracle.solve_batch(so, lo, x0, xT, gx, gu, gT, nthreads=8)
+    assert np.all(np.abs(sT - oT) <= 1e-6 * np.abs(oT)), np.abs(sT - oT).max()
+    assert np.abs(sx - osx).max() < 1e-5 and np.abs(su - osu).max() < 1e-5
+    for i in range(n):
+        assert _stats_tuple(st[i]) == _ostats_tuple(ost[i]), i
+        assert abs(st[i]["max_violation"] - ost[i].max_violation) < 1e-7
+        assert abs(st[i]["l1_violation"] - ost[i].l1_violation) < 1e-7
+    # duals of one problem
+    o1 = oracle.solve(so, lo, x0[0], xT[0], gx[0], gu[0], gT[0], want_lam=True)
+    assert np.abs(o1[3] - slam[0]).max() < 1e-5 * max(1.0, np.abs(o1[3]).max())
+
+
+def test_embedded_reference_problem(oracle, solver):
+    """The one start/target pair the reference's notebook embeds, with its Ruckig samples as the guess."""
+    import os
+    emb = np.load(os.path.join(os.path.dirname(__file__), "golden", "embedded_trajectory.npz"))
+    s = M.default_settings(); lim = M.default_limits(OFFLINE_MARGINS)
+    solver.set_limits(lim)
+    t = M.time_nodes(s)
+    T = float(emb["t_rk"][-1])
+    gx = np.zeros((19, 14)); gu = np.zeros((19, 7))
+    for k in range(19):
+        for j in range(7):
+            gx[k, j] = np.interp(t[k] * T, emb["t_rk"], emb["q_rk"][j])
+            gx[k, 7 + j] = np.interp(t[k] * T, emb["t_rk"], emb["v_rk"][j])
+            gu[k, j] = np.interp(t[k] * T, emb["t_rk"], emb["a_rk"][j])
+    x0 = gx[0].copy(); xT = np.concatenate([emb["target_q"], emb["target_v"]])
+    sx, su, sT, _, st = solver.solve(x0, xT, gx.ravel(), gu.ravel(), T)
+    o = oracle.solve(oracle.default_settings(), oracle.default_limits(OFFLINE_MARGINS), x0, xT, gx.ravel(), gu.ravel(), T)
+    assert abs(sT[0] - o[2]) <= 1e-6 * o[2] and np.abs(sx[0] - o[0]).max() < 1e-5 and np.abs(su[0] - o[1]).max() < 1e-5
+    # plausibility band of SURVEY B.4 around the reference's embedded result (parity with polympc itself is unpinned)
+    assert abs(sT[0] - 1.55469) < 0.08
+
+
+def test_batch_order_and_sharding_invariance(solver):
+    """Per-problem outputs do not depend on the batch they are solved in (bitwise): what multi-GPU sharding relies on."""
+    s, lim, x0, xT, gx, gu, gT = _problems(0, 2, 40, BENCH_MARGINS)
+    solver.set_limits(lim)
+    full = solver.solve(x0, xT, gx, gu, gT)
+    lo = solver.solve(x0[:13], xT[:13], gx[:13], gu[:13], gT[:13])
+    hi = solver.solve(x0[13:], xT[13:], gx[13:], gu[13:], gT[13:])
+    assert np.array_equal(full[0], np.concatenate([lo[0], hi[0]])) and np.array_equal(full[2], np.concatenate([lo[2], hi[2]]))
+    one = solver.solve(x0[5], xT[5], gx[5], gu[5], gT[5])
+    assert np.array_equal(one[0][0], full[0][5])
+
+
+def test_large_batch_properties(solver):
+    """mpc_benchmark size (1000): every problem terminates with a finite solution that honours the pinned initial state,
+    the final-state box up to the solver's own reported violation, and the p bounds."""
+    s, lim, x0, xT, gx, gu, gT = _problems(0, 1, 1000, BENCH_MARGINS)
+    solver.set_limits(lim)
+    sx, su, sT, _, st = solver.solve(x0, xT, gx, gu, gT)
+    assert np.isfinite(sx).all() and np.isfinite(su).all() and np.isfinite(sT).all()
+    assert set(np.unique(st["status"])) <= {1, 2}
+    assert (st["sqp_iters"] >= 1).all() and (st["qp_iters_total"] <= 1400).all()
+    sx = sx.reshape(1000, 19, 14)
+    viol = st["max_violation"]
+    assert (np.abs(sx[:, 0] - x0).max(axis=1) <= viol + 1e-12).all()
+    assert (np.abs(sx[:, -1] - xT).max(axis=1) <= 0.01 + viol + 1e-12).all()
+    assert (sT >= -viol - 1e-12).all() and (sT <= 10 + viol + 1e-12).all()
+    assert solver.last_solve_ms() > 0
+
+
+def test_sample_and_accounting_match_oracle(oracle, solver):
+    s, lim, x0, xT, gx, gu, gT = _problems(0, 4, 6, BENCH_MARGINS)
+    solver.set_limits(lim)
+    sx, su, sT, _, _ = solver.solve(x0, xT, gx, gu, gT)
+    traj, acc = solver.sample(sx, su, sT, target=xT, npts=200)
+    so = oracle.default_settings(); lo = oracle.default_limits(BENCH_MARGINS)
+    for i in range(6):
+        ot = oracle.sample_solution(so, sx[i], su[i], sT[i], 200)
+        assert np.abs(traj[i] - ot).max() < 1e-9
+        oa = oracle.account(lo, ot, xT[i])
+        assert list(acc[i]["flags"]) == list(oa.flags)
+        assert np.abs(acc[i]["mins"] - np.array(oa.mins)).max() < 1e-9 and np.abs(acc[i]["maxs"] - np.array(oa.maxs)).max() < 1e-9
+        assert np.abs(acc[i]["final_err"] - np.array(oa.final_err)).max() < 1e-9
+
+
+def test_bad_arguments_are_rejected(solver):
+    import ctypes as C
+    L = M.load_library()
+    assert L.mpcb_solve_batch(solver.h, C.c_int(-1), None, None, None, None, None, None, None, None, None, None, None, 0, None) == -2
+    assert L.mpcb_solve_batch(solver.h, C.c_int(1), None, None, None, None, None, None, None, None, None, None, None, 0, None) == -2
+    assert L.mpcb_solve_batch(solver.h, C.c_int(0), None, None, None, None, None, None, None, None, None, None, None, 0, None) == 0

@@ -1,0 +1,281 @@
+#!/usr/bin/env python3
+"""Benchmark of the hot path: solved minimum-time Panda OCPs per second (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
+
+A "step" is one pass of the hot path (mpcb_solve_batch: the whole SQP of every OCP of the batch, one kernel launch) over
+one batch of synthetic problems: the `mpc_benchmark` configuration (examples/benchmark.cpp of the reference: margins
+0.8/0.8/0.6/0.9/0.1, start at the mid-range pose at rest, random target; 1000 trajectories) per GPU.  With N > 1 (launched
+by torchrun, one rank per GPU) every rank solves its own 1000-problem shard of the global batch (no data-path
+collective; weak scaling) and the per-rank statistics are gathered with one NCCL all_gather.
+
+  value : OCPs/s with the inputs already resident in HBM (device pointers through the C ABI), CUDA events
+  e2e   : the same through the host-pointer C ABI call (pinned host buffers, H2D + D2H inside the timed region)
+  --impl reference : the CPU restatement of the reference's algorithm (oracle/, the reference itself cannot be built
+                     here: polympc/pinocchio/ruckig/Eigen are absent) on all host threads, on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MARGINS = [0.8, 0.8, 0.6, 0.9, 0.1]      # examples/benchmark.cpp:9
+WORKLOAD = "mpc_benchmark: 1000 random Panda min-time OCPs per GPU (PO=3, NS=6, 2 SQP x <=700 ADMM, pos/vel/acc/torque/height limits)"
+METRIC = "solved OCPs/sec (mpc_benchmark shape)"
+UNIT = "OCP/s"
+
+# Algorithmic FP64 work of one OCP (DESIGN.md "Work model"): structure-exploiting counts of THIS implementation
+W_IT = 2 * (18473 + 2 * 7679 + 5041 + 2 * 4856) + 6432   # one ADMM iteration: W, F^T, C, F mat-vecs + A, A^T + vector ops
+W_FAC = 63 * 78 ** 2 + 4 * 49 * 78 ** 2 + 70 * 85 ** 2 + 71 ** 3 + 120000   # sweeps (interiors + separator) + assembly
+W_LIN = 300000                                            # 19 x (RNEA derivatives + CRBA + frame Jacobian) + collocation
+W_MERIT = 35000                                           # 19 x (RNEA + FK) + residuals
+
+
+def flops_of(stats):
+    import numpy as np
+    sqp = stats["sqp_iters"].astype(np.float64)
+    admm = stats["qp_iters_total"].astype(np.float64)
+    ls = stats["ls_trials"].sum(axis=1).astype(np.float64) + 2 * sqp
+    return float((sqp * (W_LIN + W_FAC) + admm * W_IT + ls * W_MERIT).sum())
+
+
+class ClockSampler:
+    QUERY = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index = index; self.samples = []; self.stop = False; self.th = None
+
+    def _run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def __enter__(self):
+        self.th = threading.Thread(target=self._run, daemon=True); self.th.start(); return self
+
+    def __exit__(self, *a):
+        self.stop = True; self.th.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        import statistics
+        sm = [float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(s) > 2 + i and s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(self.samples)}
+
+
+def cpu_baseline(n_sample, threads):
+    """Oracle (CPU restatement, kind 'port') on `threads` host threads over the first n_sample problems of the workload."""
+    import mpc_motion_planner_b200 as M
+    from oracle import oracle_py as O
+    s = M.default_settings(); lim = M.default_limits(MARGINS)
+    x0, xT = M.generate_problems(lim, 0, 1, n_sample)
+    gx, gu, gT = M.guess_batch(s, lim, x0, xT)
+    so = O.default_settings(); lo = O.default_limits(MARGINS)
+    t0 = time.perf_counter()
+    O.solve_batch(so, lo, x0, xT, gx, gu, gT, nthreads=threads)
+    dt = time.perf_counter() - t0
+    return n_sample / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    n_sample = max(threads * 24, 48)
+    from oracle import oracle_py as O
+    O.build()
+    times = []
+    for i in range(args.warmup + args.steps):
+        v, dt = cpu_baseline(n_sample, threads)
+        if i >= args.warmup:
+            times.append(dt)
+    dt = sum(times) / len(times)
+    value = n_sample / dt
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "sample": f"first {n_sample} problems of the seed-1 batch per step"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": f"{n_sample} OCPs per step on {threads} threads (oracle/: CPU restatement; the reference binary cannot be built: polympc, pinocchio, ruckig, Eigen absent)"},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import mpc_motion_planner_b200 as M
+    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_
+        dist = dist_
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    B = args.batch
+    s = M.default_settings(); lim = M.default_limits(MARGINS)
+    # rank r owns problems [r*B, (r+1)*B) of the global seed-1 batch (generator streams are indexed by problem)
+    x0a, xTa = M.generate_problems(lim, 0, 1, B * world)
+    x0 = x0a[rank * B:(rank + 1) * B].copy(); xT = xTa[rank * B:(rank + 1) * B].copy()
+    gx, gu, gT = M.guess_batch(s, lim, x0, xT)
+    sv = M.Solver(s, lim, device=local)
+    N = sv.N
+    # ---- device-resident arm -------------------------------------------------------------------------------------
+    dx0 = torch.from_numpy(x0).to(dev); dxT = torch.from_numpy(xT).to(dev); dgx = torch.from_numpy(gx).to(dev)
+    dgu = torch.from_numpy(gu).to(dev); dgT = torch.from_numpy(gT).to(dev)
+    dsx = torch.empty_like(dgx); dsu = torch.empty_like(dgu); dsT = torch.empty_like(dgT)
+    dst = torch.zeros(B * M.capi.STATS_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step_device():
+        sv.solve_device(B, dx0.data_ptr(), dxT.data_ptr(), dgx.data_ptr(), dgu.data_ptr(), dgT.data_ptr(), 0, dsx.data_ptr(), dsu.data_ptr(),
+                        dsT.data_ptr(), 0, dst.data_ptr(), stream)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        flush.fill_(1); step_device()
+    barrier()
+    launches0 = sv.launch_count()
+    evs = []
+    with ClockSampler(local) as clk:
+        t_wall0 = time.perf_counter()
+        for _ in range(args.steps):
+            flush.fill_(1)                                   # L2 flush between timed iterations (outside the event pair)
+            a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+            a.record(); step_device(); b.record()
+            evs.append((a, b))
+        barrier()
+        t_wall = time.perf_counter() - t_wall0
+    launches = sv.launch_count() - launches0
+    ms_steps = [a.elapsed_time(b) for a, b in evs]
+    ms_total = sum(ms_steps)
+    stats = np.frombuffer(dst.cpu().numpy().tobytes(), dtype=M.capi.STATS_DTYPE)
+    flops_step = flops_of(stats)
+    sol_T = dsT.cpu().numpy()
+    # ---- end-to-end arm: host-pointer C-ABI call with pinned host buffers --------------------------------------------
+    def pinned(a):
+        t = torch.empty(a.shape, dtype=torch.float64, pin_memory=True); t.numpy()[...] = a; return t
+    hx0, hxT, hgx, hgu, hgT = pinned(x0), pinned(xT), pinned(gx), pinned(gu), pinned(gT)
+    hsx = torch.empty((B, 14 * N), dtype=torch.float64, pin_memory=True); hsu = torch.empty((B, 7 * N), dtype=torch.float64, pin_memory=True)
+    hsT = torch.empty(B, dtype=torch.float64, pin_memory=True)
+    hst = torch.empty(B * M.capi.STATS_DTYPE.itemsize, dtype=torch.uint8, pin_memory=True)
+    import ctypes as C
+    def step_host():
+        rc = sv.L.mpcb_solve_batch(sv.h, C.c_int(B), C.c_void_p(hx0.data_ptr()), C.c_void_p(hxT.data_ptr()), C.c_void_p(hgx.data_ptr()),
+                                   C.c_void_p(hgu.data_ptr()), C.c_void_p(hgT.data_ptr()), None, C.c_void_p(hsx.data_ptr()), C.c_void_p(hsu.data_ptr()),
+                                   C.c_void_p(hsT.data_ptr()), None, C.c_void_p(hst.data_ptr()), C.c_int(0), None)
+        assert rc == 0, sv.L.mpcb_last_error(sv.h)
+    step_host()
+    barrier()
+    e2e_steps = max(1, min(args.steps, 5))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_host()                                          # synchronous: returns after the D2H copies
+    barrier()
+    t_e2e = (time.perf_counter() - t0) / e2e_steps
+    assert np.array_equal(hsT.numpy(), sol_T), "host-pointer and device-pointer calls must give identical results"
+    h2d = B * (14 + 14 + 14 * N + 7 * N + 1) * 8
+    d2h = B * ((14 * N + 7 * N + 1) * 8 + M.capi.STATS_DTYPE.itemsize)
+    # ---- max over ranks + statistics gather ---------------------------------------------------------------------------
+    loc = torch.tensor([ms_total, t_e2e, flops_step, float((stats["status"] == 1).sum()), float(stats["qp_iters_total"].sum()),
+                        float(stats["sqp_iters"].sum()), float(sol_T.sum()), float(sol_T.min()), float(sol_T.max()), float(B)],
+                       dtype=torch.float64, device=dev)
+    if dist is not None:
+        allr = [torch.empty_like(loc) for _ in range(world)]
+        dist.all_gather(allr, loc)
+        allr = torch.stack(allr).cpu().numpy()
+    else:
+        allr = loc.cpu().numpy()[None]
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    ms_total_max = float(allr[:, 0].max()); t_e2e_max = float(allr[:, 1].max())
+    total_ocps = float(allr[:, 9].sum())
+    ms_per_step = ms_total_max / args.steps
+    value = total_ocps / (ms_per_step * 1e-3)
+    fp64_peak = sv.fp64_tflops()
+    achieved = flops_step / (ms_total / args.steps * 1e-3) / 1e12          # rank 0's kernel
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    algo_bytes = B * (h2d + d2h) / B
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": int(total_ocps), "seed": 1, "guess": "cubic-Hermite stand-in for Ruckig",
+                   "l2": "256 MiB buffer written between timed steps (L2 flush)", "parallelism": f"batch shards x{world}, stats all_gather"},
+        "e2e": {"value": total_ocps / t_e2e_max, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
+        "gpu_launches": int(launches),
+        "clocks": clk.summary(),
+        "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak > 0 else None,
+                     "traffic": None, "peak_source": "FP64 FMA micro-benchmark run in this process (MEASURED_PEAKS.json has no FP64 figure)",
+                     "flops_per_launch": flops_step, "kernel_ms": ms_total / args.steps,
+                     "hbm": {"achieved_gbs": algo_bytes / (ms_total / args.steps * 1e-3) / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
+                             "note": "algorithmic HBM bytes per launch = inputs + outputs; the path is not HBM-bound"}},
+        "stats": {"solved": int(allr[:, 3].sum()), "admm_iters_per_ocp": float(allr[:, 4].sum() / total_ocps), "sqp_iters_per_ocp": float(allr[:, 5].sum() / total_ocps),
+                  "mean_T": float(allr[:, 6].sum() / total_ocps), "min_T": float(allr[:, 7].min()), "max_T": float(allr[:, 8].max()),
+                  "wall_s_timed_region": t_wall, "p50_step_ms": float(sorted(ms_steps)[len(ms_steps) // 2])},
+    }
+    # single-solve latency (n = 1), device-resident
+    lat = []
+    for _ in range(5):
+        a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+        a.record()
+        sv.solve_device(1, dx0.data_ptr(), dxT.data_ptr(), dgx.data_ptr(), dgu.data_ptr(), dgT.data_ptr(), 0, dsx.data_ptr(), dsu.data_ptr(), dsT.data_ptr(), 0, dst.data_ptr(), stream)
+        b.record(); torch.cuda.synchronize(); lat.append(a.elapsed_time(b))
+    line["stats"]["p50_single_solve_latency_ms"] = float(sorted(lat)[len(lat) // 2])
+    if world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        n_sample = max(threads * 24, 48)
+        v, dt = cpu_baseline(n_sample, threads)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"first {n_sample} OCPs of the same batch, {dt:.1f} s, oracle/ (CPU restatement; reference binary unbuildable here)"}
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=1000, help="OCPs per GPU per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

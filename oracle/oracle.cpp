@@ -614,7 +614,8 @@ QPResult qp_admm(const Dims& d, const orc_settings* st, const double* zlin, cons
             A_mul(d, zlin, Jg, x.data(), Ax.data());
             AT_mul(d, zlin, Jg, yA.data(), Aty.data());
             double nAx = 0, nx = 0, nz = 0, rp = 0, rd = 0, nHx = 0, nAty = 0, nh = 0;
-            for (int i = 0; i < n; i++) { Hx[i] = Hd[i] * x[i]; if (i != ip) { Hx[i] += Ha[i] * x[ip]; Hx[ip] += Ha[i] * x[i]; } }
+            for (int i = 0; i < n; i++) Hx[i] = Hd[i] * x[i];
+            for (int i = 0; i < n; i++) if (i != ip) { Hx[i] += Ha[i] * x[ip]; Hx[ip] += Ha[i] * x[i]; }   // H = diag + p-arrow
             for (int i = 0; i < m; i++) { nAx = std::max(nAx, std::fabs(Ax[i])); nz = std::max(nz, std::fabs(zA[i])); rp = std::max(rp, std::fabs(Ax[i] - zA[i])); }
             for (int i = 0; i < n; i++) {
                 nx = std::max(nx, std::fabs(x[i])); nz = std::max(nz, std::fabs(zB[i])); rp = std::max(rp, std::fabs(x[i] - zB[i]));

@@ -22,3 +22,12 @@ $(OUT): build/mpcb_kernels.o build/mpcb_capi.o build/mpcb_planner_host.o
 	$(NVCC) -shared -o $@ $^ -cudart shared -Xlinker -rpath=$(CUDA_HOME)/lib64
 clean:
 	rm -rf build $(OUT)
+
+# Debug variant with per-phase cycle counters in the ADMM kernel (tools/phase_profile.py); not used by tests or bench.
+PROF_OUT = mpc_motion_planner_b200/libmpcb_prof.so
+prof: $(PROF_OUT)
+build/prof_kernels.o: $(SRC)/mpcb_kernels.cu $(HDR)
+	@mkdir -p build
+	$(NVCC) $(NVFLAGS) -DMPCB_PROFILE -c $< -o $@
+$(PROF_OUT): build/prof_kernels.o build/mpcb_capi.o build/mpcb_planner_host.o
+	$(NVCC) -shared -o $@ $^ -cudart shared -Xlinker -rpath=$(CUDA_HOME)/lib64

@@ -3,7 +3,8 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B]
 
-A "step" is one pass of the hot path (mpcb_solve_batch: the whole SQP of every OCP of the batch, one kernel launch) over
+A "step" is one pass of the hot path (mpcb_solve_batch: the whole SQP of every OCP of the batch; 1 + 2 x sqp_max_iter kernel
+launches: linearise/factorise stage, then per SQP iteration the ADMM kernel and the line-search/step stage) over
 one batch of synthetic problems: the `mpc_benchmark` configuration (examples/benchmark.cpp of the reference: margins
 0.8/0.8/0.6/0.9/0.1, start at the mid-range pose at rest, random target; 1000 trajectories) per GPU.  With N > 1 (launched
 by torchrun, one rank per GPU) every rank solves its own 1000-problem shard of the global batch (no data-path
@@ -161,6 +162,7 @@ def run_ours(args):
     barrier()
     launches0 = sv.launch_count()
     evs = []
+    admm_ms = []; stage_ms = []; admm_launches = 0
     with ClockSampler(local) as clk:
         t_wall0 = time.perf_counter()
         for _ in range(args.steps):
@@ -168,6 +170,8 @@ def run_ours(args):
             a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
             a.record(); step_device(); b.record()
             evs.append((a, b))
+            admm_ms.append(sv.last_kernel_ms(1)); stage_ms.append(sv.last_kernel_ms(0))      # per-launch CUDA events on the launch stream
+            admm_launches += sv.last_kernel_launches(1)
         barrier()
         t_wall = time.perf_counter() - t_wall0
     launches = sv.launch_count() - launches0
@@ -175,6 +179,7 @@ def run_ours(args):
     ms_total = sum(ms_steps)
     stats = np.frombuffer(dst.cpu().numpy().tobytes(), dtype=M.capi.STATS_DTYPE)
     flops_step = flops_of(stats)
+    flops_admm_step = float(stats["qp_iters_total"].astype(np.float64).sum()) * W_IT
     sol_T = dsT.cpu().numpy()
     # ---- end-to-end arm: host-pointer C-ABI call with pinned host buffers --------------------------------------------
     def pinned(a):
@@ -219,7 +224,11 @@ def run_ours(args):
     ms_per_step = ms_total_max / args.steps
     value = total_ocps / (ms_per_step * 1e-3)
     fp64_peak = sv.fp64_tflops()
-    achieved = flops_step / (ms_total / args.steps * 1e-3) / 1e12          # rank 0's kernel
+    achieved_step = flops_step / (ms_total / args.steps * 1e-3) / 1e12     # rank 0, all kernels of a step
+    # dominant kernel = admm_kernel: algorithmic FLOPs per launch / average launch duration (CUDA events around each launch)
+    admm_ms_launch = sum(admm_ms) / max(admm_launches, 1)
+    flops_admm_launch = flops_admm_step * args.steps / max(admm_launches, 1)
+    achieved = flops_admm_launch / (admm_ms_launch * 1e-3) / 1e12
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -236,7 +245,10 @@ def run_ours(args):
         "clocks": clk.summary(),
         "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak > 0 else None,
                      "traffic": None, "peak_source": "FP64 FMA micro-benchmark run in this process (MEASURED_PEAKS.json has no FP64 figure)",
-                     "flops_per_launch": flops_step, "kernel_ms": ms_total / args.steps,
+                     "kernel": "admm_kernel", "flops_per_launch": flops_admm_launch, "kernel_ms": admm_ms_launch,
+                     "kernel_share_of_step": sum(admm_ms) / ms_total,
+                     "step": {"flops": flops_step, "ms": ms_total / args.steps, "achieved": achieved_step,
+                              "admm_ms": sum(admm_ms) / args.steps, "sqp_stage_ms": sum(stage_ms) / args.steps},
                      "hbm": {"achieved_gbs": algo_bytes / (ms_total / args.steps * 1e-3) / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
                              "note": "algorithmic HBM bytes per launch = inputs + outputs; the path is not HBM-bound"}},
         "stats": {"solved": int(allr[:, 3].sum()), "admm_iters_per_ocp": float(allr[:, 4].sum() / total_ocps), "sqp_iters_per_ocp": float(allr[:, 5].sum() / total_ocps),

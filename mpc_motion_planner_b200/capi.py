@@ -5,7 +5,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libmpcb.so")
+# MPCB_LIB selects a debug build of the same library (e.g. libmpcb_prof.so from `make prof`); default = the product
+_LIB_PATH = os.environ.get("MPCB_LIB") or os.path.join(_HERE, "libmpcb.so")
 _lib = None
 
 
@@ -71,6 +72,9 @@ def load_library():
         L.mpcb_last_solve_ms.restype = C.c_double
         L.mpcb_measure_fp64_tflops.restype = C.c_double
         L.mpcb_launch_count.restype = C.c_longlong
+        L.mpcb_last_kernel_ms.restype = C.c_double
+        L.mpcb_last_kernel_ms.argtypes = [C.c_void_p, C.c_int]
+        L.mpcb_last_kernel_launches.argtypes = [C.c_void_p, C.c_int]
         for name in ("mpcb_last_error", "mpcb_last_solve_ms", "mpcb_measure_fp64_tflops", "mpcb_launch_count", "mpcb_destroy",
                      "mpcb_set_limits"):
             getattr(L, name).argtypes = None
@@ -208,6 +212,13 @@ class Solver:
 
     def launch_count(self):
         return self.L.mpcb_launch_count(self.h)
+
+    def last_kernel_ms(self, kind):
+        """Device time of the last solve split by kernel kind: 0 = SQP stage kernels, 1 = ADMM kernel."""
+        return self.L.mpcb_last_kernel_ms(self.h, kind)
+
+    def last_kernel_launches(self, kind):
+        return self.L.mpcb_last_kernel_launches(self.h, kind)
 
     def fp64_tflops(self):
         return self.L.mpcb_measure_fp64_tflops(self.h)

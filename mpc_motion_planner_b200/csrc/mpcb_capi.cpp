@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <string>
+#include <vector>
 
 #include "mpcb.h"
 #include "mpcb_host_util.h"
@@ -20,8 +21,15 @@ struct mpcb_handle {
     mpcb_limits lim;
     KernelConst kc;
     int grid_max = 0;
-    int* d_counter = nullptr;
-    double* d_workspace = nullptr;
+    int* d_counter = nullptr;            // one work counter per kernel launch of a chunk
+    int n_counter = 0;
+    double* d_workspace = nullptr;       // per-OCP blocks (iterate, multipliers, QP block) of one chunk
+    int ws_ocps = 0;
+    long long* d_prof = nullptr;         // 16 per-phase cycle counters (filled only by -DMPCB_PROFILE builds)
+    // per-launch timing of the last mpcb_solve_batch: event pairs and the kind of each launch (0 = SQP stage, 1 = ADMM)
+    std::vector<cudaEvent_t> kev;
+    std::vector<int> kkind;
+    int kused = 0;
     // staging buffers for MPCB_MEM_HOST calls (grown on demand)
     void* d_stage = nullptr;
     size_t stage_bytes = 0;
@@ -83,10 +91,9 @@ int mpcb_create(const mpcb_settings* s, int device, mpcb_handle** out) {
         mpcb_destroy(h);
         return MPCB_ERR_UNSUPPORTED;
     }
-    if ((e = solve_prepare()) != cudaSuccess) return fail("cudaFuncSetAttribute(solve_kernel)", e);
+    if ((e = solve_prepare()) != cudaSuccess) return fail("cudaFuncSetAttribute(solve kernels)", e);
     h->grid_max = h->sm_count;      // one CTA per SM (shared memory bound)
-    if ((e = cudaMalloc(&h->d_counter, sizeof(int))) != cudaSuccess) return fail("cudaMalloc", e);
-    if ((e = cudaMalloc(&h->d_workspace, sizeof(double) * solve_workspace_doubles_per_cta() * h->grid_max)) != cudaSuccess) return fail("cudaMalloc", e);
+    if ((e = cudaMalloc(&h->d_prof, 16 * sizeof(long long))) != cudaSuccess || (e = cudaMemset(h->d_prof, 0, 16 * sizeof(long long))) != cudaSuccess) return fail("cudaMalloc(prof)", e);
     if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
     *out = h;
     return MPCB_OK;
@@ -98,6 +105,8 @@ void mpcb_destroy(mpcb_handle* h) {
     if (h->d_counter) cudaFree(h->d_counter);
     if (h->d_workspace) cudaFree(h->d_workspace);
     if (h->d_stage) cudaFree(h->d_stage);
+    if (h->d_prof) cudaFree(h->d_prof);
+    for (cudaEvent_t e : h->kev) cudaEventDestroy(e);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     delete h;
@@ -121,6 +130,42 @@ static int ensure_stage(mpcb_handle* h, size_t bytes) {
     return MPCB_OK;
 }
 static size_t al(size_t b) { return (b + 255) / 256 * 256; }
+
+// Problems are solved in chunks of at most this many OCPs: the per-OCP workspace (QP block) is ~350 KB.
+static const int CHUNK_MAX = 4096;
+
+static int ensure_workspace(mpcb_handle* h, int ocps, int counters) {
+    if (ocps > h->ws_ocps) {
+        if (h->d_workspace) { cudaFree(h->d_workspace); h->d_workspace = nullptr; h->ws_ocps = 0; }
+        cudaError_t e = cudaMalloc(&h->d_workspace, sizeof(double) * solve_workspace_doubles_per_ocp() * (size_t)ocps);
+        if (e != cudaSuccess) { h->err = std::string("cudaMalloc(workspace): ") + cudaGetErrorString(e); return MPCB_ERR_ALLOC; }
+        h->ws_ocps = ocps;
+    }
+    if (counters > h->n_counter) {
+        if (h->d_counter) { cudaFree(h->d_counter); h->d_counter = nullptr; h->n_counter = 0; }
+        cudaError_t e = cudaMalloc(&h->d_counter, sizeof(int) * counters);
+        if (e != cudaSuccess) { h->err = std::string("cudaMalloc(counters): ") + cudaGetErrorString(e); return MPCB_ERR_ALLOC; }
+        h->n_counter = counters;
+    }
+    return MPCB_OK;
+}
+// record an event pair around one kernel launch
+static int timed_launch_begin(mpcb_handle* h, int kind, cudaStream_t stream) {
+    while ((int)h->kev.size() < 2 * (h->kused + 1)) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return -1;
+        h->kev.push_back(e);
+    }
+    if ((int)h->kkind.size() < h->kused + 1) h->kkind.resize(h->kused + 1);
+    h->kkind[h->kused] = kind;
+    return cudaEventRecord(h->kev[2 * h->kused], stream) == cudaSuccess ? 0 : -1;
+}
+static int timed_launch_end(mpcb_handle* h, cudaStream_t stream) {
+    const int rc = cudaEventRecord(h->kev[2 * h->kused + 1], stream) == cudaSuccess ? 0 : -1;
+    h->kused++;
+    h->launches++;
+    return rc;
+}
 
 int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, const double* guess_x, const double* guess_u,
                      const double* guess_T, const double* guess_lam, double* sol_x, double* sol_u, double* sol_T, double* sol_lam,
@@ -160,11 +205,35 @@ int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, 
         bp.x0 = dx0; bp.xT = dxT; bp.gx = dgx; bp.gu = dgu; bp.gT = dgT; bp.glam = dgl;
         bp.sx = dsx; bp.su = dsu; bp.sT = dsT; bp.slam = dsl; bp.stats = dst;
     }
-    const int grid = n < h->grid_max ? n : h->grid_max;
+    const int chunk = n < CHUNK_MAX ? n : CHUNK_MAX;
+    const int n_launch = 1 + 2 * h->st.sqp_max_iter;
+    { int rc = ensure_workspace(h, chunk, n_launch); if (rc) return rc; }
+    h->kused = 0;
     CK(cudaEventRecord(h->ev0, stream));
-    CK(launch_solve(h->kc, bp, n, grid, h->d_counter, h->d_workspace, stream));
+    for (int c0 = 0; c0 < n; c0 += chunk) {
+        const int nn = (n - c0) < chunk ? (n - c0) : chunk;
+        const int grid = nn < h->grid_max ? nn : h->grid_max;
+        BatchPtrs cp = bp;
+        cp.x0 += (size_t)14 * c0; cp.xT += (size_t)14 * c0; cp.gx += (size_t)14 * N * c0; cp.gu += (size_t)7 * N * c0; cp.gT += c0;
+        if (cp.glam) cp.glam += (size_t)ND * c0;
+        cp.sx += (size_t)14 * N * c0; cp.su += (size_t)7 * N * c0; cp.sT += c0;
+        if (cp.slam) cp.slam += (size_t)ND * c0;
+        if (cp.stats) cp.stats += c0;
+        CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int) * n_launch, stream));
+        int li = 0;
+        if (timed_launch_begin(h, 0, stream)) { h->err = "cudaEventRecord failed"; return MPCB_ERR_CUDA; }
+        CK(launch_sqp_stage(h->kc, cp, nn, 0, grid, h->d_counter + li++, h->d_workspace, stream));
+        timed_launch_end(h, stream);
+        for (int it = 1; it <= h->st.sqp_max_iter; it++) {
+            if (timed_launch_begin(h, 1, stream)) { h->err = "cudaEventRecord failed"; return MPCB_ERR_CUDA; }
+            CK(launch_admm(h->kc, nn, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
+            timed_launch_end(h, stream);
+            if (timed_launch_begin(h, 0, stream)) { h->err = "cudaEventRecord failed"; return MPCB_ERR_CUDA; }
+            CK(launch_sqp_stage(h->kc, cp, nn, it, grid, h->d_counter + li++, h->d_workspace, stream));
+            timed_launch_end(h, stream);
+        }
+    }
     CK(cudaEventRecord(h->ev1, stream));
-    h->launches += 1;
     h->timed = true; h->timed_stream = stream;
     if (mem == MPCB_MEM_HOST) {
         CK(cudaMemcpyAsync(sol_x, bp.sx, bgx, cudaMemcpyDeviceToHost, stream));
@@ -229,6 +298,34 @@ double mpcb_last_solve_ms(mpcb_handle* h) {
     return (double)ms;
 }
 long long mpcb_launch_count(const mpcb_handle* h) { return h ? h->launches : 0; }
+
+double mpcb_last_kernel_ms(mpcb_handle* h, int kind) {
+    if (!h || !h->timed) return -1.0;
+    cudaSetDevice(h->device);
+    if (cudaEventSynchronize(h->ev1) != cudaSuccess) return -1.0;
+    double total = 0;
+    for (int i = 0; i < h->kused; i++) {
+        if (h->kkind[i] != kind) continue;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, h->kev[2 * i], h->kev[2 * i + 1]) != cudaSuccess) return -1.0;
+        total += ms;
+    }
+    return total;
+}
+int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out16, int reset) {
+    if (!h || !out16) return MPCB_ERR_BAD_ARG;
+    CK(cudaSetDevice(h->device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(out16, h->d_prof, 16 * sizeof(long long), cudaMemcpyDeviceToHost));
+    if (reset) CK(cudaMemset(h->d_prof, 0, 16 * sizeof(long long)));
+    return MPCB_OK;
+}
+int mpcb_last_kernel_launches(const mpcb_handle* h, int kind) {
+    if (!h) return 0;
+    int c = 0;
+    for (int i = 0; i < h->kused; i++) c += (h->kkind[i] == kind);
+    return c;
+}
 
 double mpcb_measure_fp64_tflops(mpcb_handle* h) {
     if (!h) return -1.0;

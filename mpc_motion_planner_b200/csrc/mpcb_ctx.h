@@ -24,10 +24,14 @@ constexpr int NT = 512;   // threads per CTA
 #define MPCB_DRIVER_ARGS c, tsv
 #define MPCB_PHASE(...)                       \
     for (int tid = 0; tid < NT; ++tid) {      \
-        TS<SH>& ts = tsv[tid];                \
+        auto& ts = tsv[tid];                  \
         (void)ts;                             \
         __VA_ARGS__;                          \
     }
+// a phase that needs no CTA barrier after it on the device (the next phase only exchanges registers inside a warp)
+#define MPCB_PHASE_NS(...) MPCB_PHASE(__VA_ARGS__)
+// value of `field` in the per-thread state of lane (tid ^ k)
+#define MPCB_PEER(field, k) (tsv[tid ^ (k)].field)
 #else
 #define MPCB_DEV __device__ __forceinline__
 #define MPCB_DRIVER_PARAMS(SH) Ctx<SH>& c, TS<SH>& ts, const int tid
@@ -37,6 +41,11 @@ constexpr int NT = 512;   // threads per CTA
         __VA_ARGS__;     \
         __syncthreads(); \
     }
+#define MPCB_PHASE_NS(...) \
+    {                      \
+        __VA_ARGS__;       \
+    }
+#define MPCB_PEER(field, k) __shfl_xor_sync(0xffffffffu, ts.field, k)
 #endif
 
 // uniform double scalars in shared memory

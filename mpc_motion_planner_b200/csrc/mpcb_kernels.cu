@@ -1,6 +1,8 @@
 // CUDA kernels (sm_100a) of the batched OCP solver and their launchers.
-//   solve_kernel   : persistent CTAs, one OCP per CTA at a time; the whole SQP (linearise, factorise, <=700 ADMM
-//                    iterations, line search) runs out of shared memory -- phases in mpcb_qp.h / mpcb_admm.h / mpcb_sqp.h
+//   sqp_stage_kernel: persistent CTAs, one OCP per CTA at a time: linearise + factorise (+ line search and step of the
+//                    previous SQP iteration) out of shared memory -- phases in mpcb_qp.h / mpcb_sqp.h / mpcb_export.h
+//   admm_kernel    : the hot loop, <= 700 box-ADMM iterations per QP with the interior inverses held in registers
+//                    (mpcb_admm.h); QP data handed over through a per-OCP block in global memory
 //   sample_kernel  : read-out + benchmark accounting (get_MPC_trajectory<N>, /root/reference/mpc_solver/motionPlanner.hpp:99-116;
 //                    examples/benchmark.cpp:118-194)
 //   fp64_peak_kernel: FP64 FMA throughput micro-benchmark (roofline denominator)
@@ -12,16 +14,37 @@
 
 namespace mpcb {
 
+// Per-OCP workspace in global memory: iterate z (kernel order) | multipliers | flags | QP block (struct AL).
+template <class SH>
+struct WS {
+    static constexpr int Z = 0, LAM = SH::VP, FLAGS = LAM + SH::NDUAL + 8, QB = FLAGS + 4;
+    static constexpr size_t STRIDE = (size_t)QB + AL<SH>::QPBLOCK;
+};
+
+template <class SH>
+__device__ __forceinline__ void bind_problem(Ctx<SH>& c, Problem& pb, const KernelConst& kc, const BatchPtrs& bp, double* ws, int i) {
+    c.z = ws + WS<SH>::Z;
+    c.lam = ws + WS<SH>::LAM;
+    pb.limtab = kc.limtab;
+    pb.x0 = bp.x0 + (size_t)14 * i; pb.xT = bp.xT + (size_t)14 * i;
+    pb.gx = bp.gx + (size_t)14 * SH::NN * i; pb.gu = bp.gu + (size_t)7 * SH::NN * i;
+    pb.glam = bp.glam ? bp.glam + (size_t)SH::NDUAL * i : nullptr;
+    pb.gT = bp.gT[i];
+    pb.sx = bp.sx + (size_t)14 * SH::NN * i; pb.su = bp.su + (size_t)7 * SH::NN * i; pb.sT = bp.sT + i;
+    pb.slam = bp.slam ? bp.slam + (size_t)SH::NDUAL * i : nullptr;
+    pb.stats = bp.stats ? bp.stats + i : nullptr;
+}
+
+// stage kernel: it == 0 -> stage_pre, it >= 1 -> stage_post of SQP iteration `it`
 template <class SH>
 __global__ void __launch_bounds__(NT, 1)
-solve_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, const int n, int* __restrict__ counter, double* __restrict__ workspace) {
+sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, const int n, const int it, int* __restrict__ counter,
+                 double* __restrict__ workspace) {
     extern __shared__ double smem[];
     __shared__ int s_next;
     const int tid = threadIdx.x;
     Ctx<SH> c;
     c.bind(smem);
-    c.z = workspace + (size_t)blockIdx.x * (SH::VP + SH::NDUAL + 8);
-    c.lam = c.z + SH::VP;
     c.st = &kc.st;
     c.cheb = &kc.cheb;
     TS<SH> ts;
@@ -32,16 +55,38 @@ solve_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, const i
         const int i = s_next;
         __syncthreads();
         if (i >= n) break;
+        double* ws = workspace + WS<SH>::STRIDE * i;
+        int* flags = reinterpret_cast<int*>(ws + WS<SH>::FLAGS);
+        if (it > 0 && flags[0]) continue;          // finished in an earlier SQP iteration
         Problem pb;
-        pb.limtab = kc.limtab;
-        pb.x0 = bp.x0 + (size_t)14 * i; pb.xT = bp.xT + (size_t)14 * i;
-        pb.gx = bp.gx + (size_t)14 * SH::NN * i; pb.gu = bp.gu + (size_t)7 * SH::NN * i;
-        pb.glam = bp.glam ? bp.glam + (size_t)SH::NDUAL * i : nullptr;
-        pb.gT = bp.gT[i];
-        pb.sx = bp.sx + (size_t)14 * SH::NN * i; pb.su = bp.su + (size_t)7 * SH::NN * i; pb.sT = bp.sT + i;
-        pb.slam = bp.slam ? bp.slam + (size_t)SH::NDUAL * i : nullptr;
-        pb.stats = bp.stats ? bp.stats + i : nullptr;
-        solve_ocp<SH>(c, ts, tid, pb);
+        bind_problem(c, pb, kc, bp, ws, i);
+        if (it == 0) stage_pre<SH>(c, ts, tid, pb, ws + WS<SH>::QB, flags);
+        else stage_post<SH>(c, ts, tid, pb, ws + WS<SH>::QB, flags, it);
+    }
+}
+
+// the hot kernel: <= qp_max_iter box-ADMM iterations of one QP per CTA at a time
+template <class SH>
+__global__ void __launch_bounds__(NT, 1)
+admm_kernel(const __grid_constant__ KernelConst kc, const int n, int* __restrict__ counter, double* __restrict__ workspace, long long* prof) {
+    extern __shared__ double smem[];
+    __shared__ int s_next;
+    const int tid = threadIdx.x;
+    ACtx<SH> c;
+    c.bind(smem);
+    c.st = &kc.st;
+    c.prof = prof;
+    ATS<SH> ts;
+    for (;;) {
+        if (tid == 0) s_next = atomicAdd(counter, 1);
+        __syncthreads();
+        const int i = s_next;
+        __syncthreads();
+        if (i >= n) break;
+        double* ws = workspace + WS<SH>::STRIDE * i;
+        if (reinterpret_cast<const int*>(ws + WS<SH>::FLAGS)[0]) continue;
+        c.g = ws + WS<SH>::QB;
+        admm_run<SH>(c, ts, tid);
     }
 }
 
@@ -142,16 +187,20 @@ __global__ void fp64_peak_kernel(double* out, int iters) {
 // ---- launchers -------------------------------------------------------------------------------------------------------
 typedef Shape<3, 6> SH36;
 
-size_t solve_smem_bytes() { return Layout<SH36>::BYTES; }
-size_t solve_workspace_doubles_per_cta() { return SH36::VP + SH36::NDUAL + 8; }
+size_t solve_smem_bytes() { return Layout<SH36>::BYTES > AL<SH36>::BYTES ? Layout<SH36>::BYTES : AL<SH36>::BYTES; }
+size_t solve_workspace_doubles_per_ocp() { return WS<SH36>::STRIDE; }
 
 cudaError_t solve_prepare() {
-    return cudaFuncSetAttribute(solve_kernel<SH36>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Layout<SH36>::BYTES);
-}
-cudaError_t launch_solve(const KernelConst& kc, const BatchPtrs& bp, int n, int grid, int* counter, double* workspace, cudaStream_t stream) {
-    cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
+    cudaError_t e = cudaFuncSetAttribute(sqp_stage_kernel<SH36>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Layout<SH36>::BYTES);
     if (e != cudaSuccess) return e;
-    solve_kernel<SH36><<<grid, NT, Layout<SH36>::BYTES, stream>>>(kc, bp, n, counter, workspace);
+    return cudaFuncSetAttribute(admm_kernel<SH36>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AL<SH36>::BYTES);
+}
+cudaError_t launch_sqp_stage(const KernelConst& kc, const BatchPtrs& bp, int n, int it, int grid, int* counter, double* workspace, cudaStream_t stream) {
+    sqp_stage_kernel<SH36><<<grid, NT, Layout<SH36>::BYTES, stream>>>(kc, bp, n, it, counter, workspace);
+    return cudaGetLastError();
+}
+cudaError_t launch_admm(const KernelConst& kc, int n, int grid, int* counter, double* workspace, long long* prof, cudaStream_t stream) {
+    admm_kernel<SH36><<<grid, NT, AL<SH36>::BYTES, stream>>>(kc, n, counter, workspace, prof);
     return cudaGetLastError();
 }
 cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double* su, const double* sT, const double* target, int npts,

@@ -22,9 +22,12 @@ struct BatchPtrs {
 };
 
 size_t solve_smem_bytes();
-size_t solve_workspace_doubles_per_cta();
+size_t solve_workspace_doubles_per_ocp();
 cudaError_t solve_prepare();
-cudaError_t launch_solve(const KernelConst& kc, const BatchPtrs& bp, int n, int grid, int* counter, double* workspace, cudaStream_t stream);
+// it == 0: load + linearise + factorise; it >= 1: line search / step of SQP iteration it (+ next linearisation)
+cudaError_t launch_sqp_stage(const KernelConst& kc, const BatchPtrs& bp, int n, int it, int grid, int* counter, double* workspace, cudaStream_t stream);
+// prof: 16 cycle counters accumulated by CTA 0 in MPCB_PROFILE builds (may be null)
+cudaError_t launch_admm(const KernelConst& kc, int n, int grid, int* counter, double* workspace, long long* prof, cudaStream_t stream);
 cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double* su, const double* sT, const double* target, int npts,
                           double* traj, mpcb_account* acc, int n, int grid, cudaStream_t stream);
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream);

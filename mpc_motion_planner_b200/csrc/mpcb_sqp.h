@@ -4,7 +4,7 @@
 //   * settings from MotionPlanner's constructor            (mpc_solver/motionPlanner.cpp:15-20)
 // and the guess/solution plumbing of MotionPlanner::warm_start_RK / solve_trajectory (motionPlanner.cpp:156-207).
 #pragma once
-#include "mpcb_admm.h"
+#include "mpcb_export.h"
 
 namespace mpcb {
 
@@ -151,65 +151,80 @@ MPCB_DEV void sqp_store(Ctx<SH>& c, TS<SH>& ts, int tid, const Problem& pb) {
     if (tid < SH::NA && pb.slam) pb.slam[tid] = c.lam[tid];
 }
 
-// The whole solve of one OCP.  `stats` is written by thread 0 only.
+// The solve of one OCP is cut into stages that run as separate kernels (each with its own register budget):
+//   stage_pre   : load the guess, linearise, factorise, export the QP block            (once)
+//   admm_run    : the box-ADMM iterations of the QP (mpcb_admm.h)                      (once per SQP iteration)
+//   stage_post  : line search + step + termination test of SQP iteration `it`; then either the next
+//                 linearisation/factorisation/export, or the final store               (once per SQP iteration)
+// `flags[0]` (global, per OCP) is set to 1 when the OCP is finished; later stages skip it.  `stats` is written by thread 0.
 template <class SH>
-MPCB_DEV void solve_ocp(MPCB_DRIVER_PARAMS(SH), const Problem& pb) {
-    const mpcb_settings& st = *c.st;
+MPCB_DEV void stage_pre(MPCB_DRIVER_PARAMS(SH), const Problem& pb, double* qb, int* flags) {
     mpcb_stats* S = pb.stats;
     MPCB_PHASE(sqp_load_a(c, tid, pb));
     MPCB_PHASE(sqp_load_b(c, ts, tid, pb));
-    MPCB_PHASE(if (tid == 0 && S) { memset(S, 0, sizeof(mpcb_stats)); S->status = 2; });
+    MPCB_PHASE(if (tid == 0) { flags[0] = 0; if (S) { memset(S, 0, sizeof(mpcb_stats)); S->status = 2; } });
     linearise<SH>(MPCB_DRIVER_ARGS);
-    for (int it = 1; it <= st.sqp_max_iter; it++) {
-        solve_qp<SH>(MPCB_DRIVER_ARGS);
-        MPCB_PHASE(sqp_mu(c, tid));
-        violation<SH>(MPCB_DRIVER_ARGS, 0.0, false);
-        MPCB_PHASE(if (tid == 0) {
-            const double mu = umax_get(c.umax + UM_B), l1 = c.scal[SC_V_L1];
-            c.umax[UM_B] = 0;
-            c.scal[SC_MU] = mu;
-            c.scal[SC_PHI0] = c.z[SH::IP] + mu * l1;
-            c.scal[SC_DPHI] = c.qp_p[SH::IP] - mu * l1;      // grad f . p = p_p  (cost = p)
-            c.scal[SC_ALPHA] = 1.0;
-            c.isc[IS_LS_ACCEPT] = 0;
-            if (S) {
-                S->qp_iters_total += (int)c.isc[IS_QP_ITERS];
-                if (it <= 4) { S->qp_status[it - 1] = (int)c.isc[IS_QP_STATUS]; S->qp_iters[it - 1] = (int)c.isc[IS_QP_ITERS]; }
-            }
-        });
-        // step_size_selection_impl: at most line_search_max_iter-1 trials; the last alpha is returned even if rejected
-        int trials = 0;
-        for (int i = 1; i < st.line_search_max_iter; i++) {
-            trials++;
-            const double alpha = c.scal[SC_ALPHA];
-            violation<SH>(MPCB_DRIVER_ARGS, alpha, true);
-            MPCB_PHASE(if (tid == 0) {
-                const double a = c.scal[SC_ALPHA];
-                const double phis = (c.z[SH::IP] + a * c.qp_p[SH::IP]) + c.scal[SC_MU] * c.scal[SC_V_L1];
-                if (phis <= c.scal[SC_PHI0] + a * st.sqp_eta * c.scal[SC_DPHI]) c.isc[IS_LS_ACCEPT] = 1;
-                else c.scal[SC_ALPHA] = st.sqp_tau * a;
-            });
-            if (c.isc[IS_LS_ACCEPT]) break;
+    factorise<SH>(MPCB_DRIVER_ARGS);
+    export_qp<SH>(MPCB_DRIVER_ARGS, qb);
+}
+
+template <class SH>
+MPCB_DEV void stage_post(MPCB_DRIVER_PARAMS(SH), const Problem& pb, double* qb, int* flags, const int it) {
+    const mpcb_settings& st = *c.st;
+    mpcb_stats* S = pb.stats;
+    MPCB_PHASE(sqp_load_a(c, tid, pb));
+    MPCB_PHASE(import_qp(c, tid, qb));
+    MPCB_PHASE(sqp_mu(c, tid));
+    violation<SH>(MPCB_DRIVER_ARGS, 0.0, false);
+    MPCB_PHASE(if (tid == 0) {
+        const double mu = umax_get(c.umax + UM_B), l1 = c.scal[SC_V_L1];
+        c.umax[UM_B] = 0;
+        c.scal[SC_MU] = mu;
+        c.scal[SC_PHI0] = c.z[SH::IP] + mu * l1;
+        c.scal[SC_DPHI] = c.qp_p[SH::IP] - mu * l1;      // grad f . p = p_p  (cost = p)
+        c.scal[SC_ALPHA] = 1.0;
+        c.isc[IS_LS_ACCEPT] = 0;
+        if (S) {
+            S->qp_iters_total += (int)c.isc[IS_QP_ITERS];
+            if (it <= 4) { S->qp_status[it - 1] = (int)c.isc[IS_QP_STATUS]; S->qp_iters[it - 1] = (int)c.isc[IS_QP_ITERS]; }
         }
+    });
+    // step_size_selection_impl: at most line_search_max_iter-1 trials; the last alpha is returned even if rejected
+    int trials = 0;
+    for (int i = 1; i < st.line_search_max_iter; i++) {
+        trials++;
         const double alpha = c.scal[SC_ALPHA];
-        MPCB_PHASE(sqp_step(c, tid, alpha));
-        violation<SH>(MPCB_DRIVER_ARGS, 0.0, false);
+        violation<SH>(MPCB_DRIVER_ARGS, alpha, true);
         MPCB_PHASE(if (tid == 0) {
-            const double pn = umax_get(c.umax + UM_A), dn = umax_get(c.umax + UM_B);
-            c.umax[UM_A] = 0; c.umax[UM_B] = 0;
-            const bool done = alpha * pn <= st.sqp_eps_prim && alpha * dn <= st.sqp_eps_dual && c.scal[SC_V_LINF] <= st.sqp_eps_prim;
-            c.isc[IS_SQP_DONE] = done ? 1 : 0;
-            if (S) {
-                S->sqp_iters = it; S->primal_step_norm = alpha * pn; S->dual_step_norm = alpha * dn;
-                S->max_violation = c.scal[SC_V_LINF]; S->l1_violation = c.scal[SC_V_L1]; S->cost = c.z[SH::IP];
-                if (it <= 4) { S->alpha[it - 1] = alpha; S->ls_trials[it - 1] = trials; }
-                if (done) S->status = 1;
-            }
+            const double a = c.scal[SC_ALPHA];
+            const double phis = (c.z[SH::IP] + a * c.qp_p[SH::IP]) + c.scal[SC_MU] * c.scal[SC_V_L1];
+            if (phis <= c.scal[SC_PHI0] + a * st.sqp_eta * c.scal[SC_DPHI]) c.isc[IS_LS_ACCEPT] = 1;
+            else c.scal[SC_ALPHA] = st.sqp_tau * a;
         });
-        if (c.isc[IS_SQP_DONE]) break;
-        if (it < st.sqp_max_iter) linearise<SH>(MPCB_DRIVER_ARGS);   // skipped after the last step
+        if (c.isc[IS_LS_ACCEPT]) break;
     }
-    MPCB_PHASE(sqp_store(c, ts, tid, pb));
+    const double alpha = c.scal[SC_ALPHA];
+    MPCB_PHASE(sqp_step(c, tid, alpha));
+    violation<SH>(MPCB_DRIVER_ARGS, 0.0, false);
+    MPCB_PHASE(if (tid == 0) {
+        const double pn = umax_get(c.umax + UM_A), dn = umax_get(c.umax + UM_B);
+        c.umax[UM_A] = 0; c.umax[UM_B] = 0;
+        const bool done = alpha * pn <= st.sqp_eps_prim && alpha * dn <= st.sqp_eps_dual && c.scal[SC_V_LINF] <= st.sqp_eps_prim;
+        c.isc[IS_SQP_DONE] = done ? 1 : 0;
+        if (S) {
+            S->sqp_iters = it; S->primal_step_norm = alpha * pn; S->dual_step_norm = alpha * dn;
+            S->max_violation = c.scal[SC_V_LINF]; S->l1_violation = c.scal[SC_V_L1]; S->cost = c.z[SH::IP];
+            if (it <= 4) { S->alpha[it - 1] = alpha; S->ls_trials[it - 1] = trials; }
+            if (done) S->status = 1;
+        }
+    });
+    if (c.isc[IS_SQP_DONE] || it >= st.sqp_max_iter) {      // no re-linearisation after the last step
+        MPCB_PHASE({ sqp_store(c, ts, tid, pb); if (tid == 0) flags[0] = 1; });
+        return;
+    }
+    linearise<SH>(MPCB_DRIVER_ARGS);
+    factorise<SH>(MPCB_DRIVER_ARGS);
+    export_qp<SH>(MPCB_DRIVER_ARGS, qb);
 }
 
 }  // namespace mpcb

@@ -13,24 +13,33 @@ typedef Shape<3, 6> SH36;
 
 template <class SH>
 struct Emu {
-    std::vector<double> smem, z, lam;
+    std::vector<double> smem, z, lam, qb, asmem;
     std::vector<TS<SH>> tsv;
+    std::vector<ATS<SH>> atsv;
     Ctx<SH> c;
+    ACtx<SH> ac;
     ChebConst cheb;
     double limtab[40];
-    Emu(const mpcb_settings* st, const mpcb_limits* lim) : smem(Layout<SH>::TOTAL, 0.0), z(SH::VP, 0.0), lam(SH::NDUAL + 8, 0.0), tsv(NT) {
+    int flags[2];
+    Emu(const mpcb_settings* st, const mpcb_limits* lim)
+        : smem(Layout<SH>::TOTAL, 0.0), z(SH::VP, 0.0), lam(SH::NDUAL + 8, 0.0), qb(AL<SH>::QPBLOCK, 0.0), asmem(AL<SH>::TOTAL, 0.0), tsv(NT), atsv(NT) {
         mpcb_fill_cheb(SH::PO, SH::NS, &cheb);
         fill_limtab(lim, limtab);
         c.bind(smem.data());
         c.z = z.data(); c.lam = lam.data(); c.st = st; c.cheb = &cheb;
+        ac.bind(asmem.data());
+        ac.st = st; ac.g = qb.data();
         std::memset(tsv.data(), 0, sizeof(TS<SH>) * NT);
+        std::memset(atsv.data(), 0, sizeof(ATS<SH>) * NT);
         for (int tid = 0; tid < NT; tid++) setup_roles(c, tsv[tid], tid);
+        flags[0] = flags[1] = 0;
     }
 };
 
 extern "C" {
 
 int emul_smem_bytes() { return (int)Layout<SH36>::BYTES; }
+int emul_admm_smem_bytes() { return (int)AL<SH36>::BYTES; }
 
 int emul_solve(const mpcb_settings* st, const mpcb_limits* lim, int n, const double* x0, const double* xT, const double* gx,
                const double* gu, const double* gT, const double* glam, double* sx, double* su, double* sT, double* slam,
@@ -47,36 +56,55 @@ int emul_solve(const mpcb_settings* st, const mpcb_limits* lim, int n, const dou
         pb.sx = sx + (size_t)14 * SH::NN * i; pb.su = su + (size_t)7 * SH::NN * i; pb.sT = sT + i;
         pb.slam = slam ? slam + (size_t)SH::NDUAL * i : nullptr;
         pb.stats = stats ? stats + i : nullptr;
-        solve_ocp<SH>(e.c, e.tsv.data(), pb);
+        // the same kernel sequence mpcb_solve_batch launches
+        stage_pre<SH>(e.c, e.tsv.data(), pb, e.qb.data(), e.flags);
+        for (int it = 1; it <= st->sqp_max_iter; it++) {
+            if (e.flags[0]) break;
+            admm_run<SH>(e.ac, e.atsv.data());
+            stage_post<SH>(e.c, e.tsv.data(), pb, e.qb.data(), e.flags, it);
+        }
     }
     return 0;
 }
 
-// Debug entry: linearise at (z, lam) given in polympc order, factorise, and apply S^-1 to `rhs` (polympc order).
+// Debug entry: linearise at (z, lam) given in polympc order, factorise, export, and apply S^-1 to `rhs` (polympc order)
+// with the ADMM kernel's own solve phases (B, B', C, D).
 int emul_kkt_apply(const mpcb_settings* st, const mpcb_limits* lim, const double* x0, const double* xT, const double* zext,
                    const double* lamext, const double* rhs, double* out, double* rhoA, double* rhoB) {
     typedef SH36 SH;
+    typedef AL<SH> L;
     Emu<SH> e(st, lim);
-    Ctx<SH>& c = e.c;
-    TS<SH>* tsv = e.tsv.data();
     std::vector<double> gx(zext, zext + 14 * SH::NN), gu(zext + 14 * SH::NN, zext + 21 * SH::NN), dummy(SH::NVAR + SH::NDUAL);
     Problem pb;
     pb.limtab = e.limtab; pb.x0 = x0; pb.xT = xT; pb.gx = gx.data(); pb.gu = gu.data(); pb.gT = zext[SH::NVAR - 1]; pb.glam = lamext;
     pb.sx = pb.su = pb.sT = dummy.data(); pb.slam = nullptr; pb.stats = nullptr;
-    MPCB_PHASE(sqp_load_a(c, tid, pb));
-    MPCB_PHASE(sqp_load_b(c, ts, tid, pb));
-    linearise<SH>(c, tsv);
-    factorise<SH>(c, tsv);
-    for (int tid = 0; tid < SH::NVAR; tid++) {
-        c.rhs[tid] = rhs[ext_index<SH>(tsv[tid].vk, tsv[tid].vcomp)];
-        rhoB[ext_index<SH>(tsv[tid].vk, tsv[tid].vcomp)] = tsv[tid].rhoB;
+    stage_pre<SH>(e.c, e.tsv.data(), pb, e.qb.data(), e.flags);
+    for (int tid = 0; tid < SH::NVAR; tid++) rhoB[ext_index<SH>(e.tsv[tid].vk, e.tsv[tid].vcomp)] = e.tsv[tid].rhoB;
+    for (int r = 0; r < SH::NA; r++) rhoA[r] = e.tsv[r].rho;
+    ACtx<SH>& c = e.ac;
+    ATS<SH>* tsv = e.atsv.data();
+    MPCB_PHASE(a_load(c, ts, tid));
+    for (int i = 0; i <= L::IP; i++) {
+        int k, comp;
+        if (L::decode(i, k, comp)) c.rhs[i] = rhs[ext_index<SH>(k, comp)];
     }
-    for (int r = 0; r < SH::NA; r++) rhoA[r] = tsv[r].rho;
-    for (int j = 0; j < 32; j++) c.psum[j] = 0;
-    MPCB_PHASE(admm_solve1(c, ts, tid));
-    MPCB_PHASE(admm_solve2(c, tid));
-    MPCB_PHASE(admm_solve3(c, ts, tid));
-    for (int tid = 0; tid < SH::NVAR; tid++) out[ext_index<SH>(tsv[tid].vk, tsv[tid].vcomp)] = c.xt[tid];
+    MPCB_PHASE_NS(b_interior(c, ts, tid));
+    MPCB_PHASE({ const double o = MPCB_PEER(acc, 1); ts.t = wrole<SH>(tid).paired ? ts.acc + o : ts.acc; });
+    MPCB_PHASE(b_seprhs(c, tid));
+    MPCB_PHASE_NS(c_separator(c, ts, tid));
+    MPCB_PHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
+    MPCB_PHASE({ const double s4 = ts.acc2 + MPCB_PEER(acc2, 2); if (tid < 4 * SH::NB && (tid & 3) == 0) c.xt[L::sepidx(tid >> 2)] = s4; });
+    MPCB_PHASE_NS(d_interior(c, ts, tid));
+    MPCB_PHASE({
+        const double o = MPCB_PEER(acc, 1);
+        const WRole r = wrole<SH>(tid);
+        const double fx = r.paired ? ts.acc + o : ts.acc;
+        if (r.valid && r.half == 0) c.xt[r.out] = ts.t - fx;
+    });
+    for (int i = 0; i <= L::IP; i++) {
+        int k, comp;
+        if (L::decode(i, k, comp)) out[ext_index<SH>(k, comp)] = c.xt[i];
+    }
     return 0;
 }
 

@@ -1,0 +1,36 @@
+#!/usr/bin/env python3
+"""Per-phase SM-cycle breakdown of the ADMM kernel (debug build `make prof`, -DMPCB_PROFILE).
+
+    make prof && MPCB_LIB=mpc_motion_planner_b200/libmpcb_prof.so python tools/phase_profile.py [n]
+
+Thread 0 of CTA 0 accumulates clock64() deltas after every phase; the numbers are cycles per ADMM iteration of one OCP
+with all SMs busy (n >= SM count).  Not a bench value (the hooks cost a few cycles per phase)."""
+import ctypes as C
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import mpc_motion_planner_b200 as M
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 148
+margins = [0.8, 0.8, 0.6, 0.9, 0.1]
+s = M.default_settings(); lim = M.default_limits(margins)
+x0, xT = M.generate_problems(lim, 0, 1, n)
+gx, gu, gT = M.guess_batch(s, lim, x0, xT)
+sv = M.Solver(s, lim, device=0)
+out = (C.c_longlong * 16)()
+sv.solve(x0, xT, gx, gu, gT)
+sv.L.mpcb_debug_phase_cycles(sv.h, out, 1)
+sx, su, sT, _, st = sv.solve(x0, xT, gx, gu, gT)
+sv.L.mpcb_debug_phase_cycles(sv.h, out, 1)
+names = ["load", "A rhs", "B interior W/F^T", "B' separator rhs", "C separator solve", "D interior back-subst", "E row/box update",
+         "residual test", "store"]
+cta0_ocps = max(1, round(n / 148))          # CTA 0 handles about n/148 OCPs per ADMM launch
+iters = 2 * 700.0 * cta0_ocps
+tot = sum(out[i] for i in range(1, 8))
+print(f"n={n}  admm kernel ms={sv.last_kernel_ms(1):.3f}  stage ms={sv.last_kernel_ms(0):.3f}  (cycles below: CTA 0, ~{cta0_ocps} OCP(s) x 2 QPs)")
+for i, nm in enumerate(names):
+    per = out[i] / iters if 1 <= i <= 7 else out[i] / (2.0 * cta0_ocps)
+    print(f"  {nm:26s} {out[i]:14d} cycles   {per:10.1f} per {'iteration' if 1 <= i <= 7 else 'QP'}")
+print(f"  iteration total            {tot / iters:10.1f} cycles")

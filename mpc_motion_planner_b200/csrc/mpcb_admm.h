@@ -13,8 +13,9 @@
 //     memory in conflict-free layouts; shared memory delivers 16 doubles/clk against 64 FMA/clk of the FP64 pipe, so
 //     everything that can live in registers does;
 //   * row r's (z_A, y_A, l, u, rho) and variable i's (x, z_b, y_b, lb, ub, rho_b) live in registers of thread r / i;
-//   * vectors use the "padded node order": index(k, comp) = 64 s + 21 j + comp with s = min(k/3, 5), j = k - 3 s, p at 404;
-//     every segment interior and every junction state is contiguous and starts on an even index (16-byte loads).
+//   * vectors use the "padded node order": index(k, comp) = 66 s + 21 j + comp with s = min(k/3, 5), j = k - 3 s, p at 414;
+//     every segment interior and every junction state is contiguous and starts on an even index (16-byte loads); the
+//     segment stride 66 (= 4 banks mod 32) keeps the broadcast loads of two segments in one warp on different banks.
 // The QP data arrives from the factorisation kernel through a per-OCP block in global memory (layout: struct AL).
 #pragma once
 #include "mpcb_ctx.h"
@@ -24,13 +25,14 @@ namespace mpcb {
 template <class SH>
 struct AL {
     static_assert(SH::PO == 3 && SH::NS == 6, "the ADMM kernel's thread mapping is specialised for POLY_ORDER=3, NUM_SEG=6");
-    static constexpr int NV = 408, IP = 404;           // padded node order
+    static constexpr int SEG = 66, NV = 416, IP = 414;  // padded node order: segment stride, length, index of p
     static constexpr int WREG = 32;                    // W coefficients per thread held in registers
     // ---- shared-memory image (copied verbatim from the global QP block) --------------------------------------------
     static constexpr int I_WOVM = 0;                   // [18][224]  columns 32..49 of the middle-segment rows
     static constexpr int I_WOV5 = I_WOVM + 18 * 224;   // [4][160]   tail columns of the last segment's half rows
     static constexpr int I_F = I_WOV5 + 4 * 160;       // F_s column-major with odd leading dimension
-    static constexpr int FSZ = 15 * 63 + 4 * 29 * 49 + 15 * 71 + 2;
+    static constexpr int FMID = 29 * 49 + 4;            // middle F_s padded so that consecutive segments continue the bank sequence
+    static constexpr int FSZ = 15 * 63 + 4 * FMID + 15 * 71;
     static constexpr int I_C = I_F + FSZ;              // [18][284]  C^-1, 4 lanes per row
     static constexpr int I_JG = I_C + 18 * 284;        // 19 nodes x (8 x 22), node stride 177
     static constexpr int JGS = 177;
@@ -40,8 +42,9 @@ struct AL {
     static constexpr int I_DT = I_PCOL + 256;          // D (16) | -ts*pbar | pad
     static constexpr int IMG = I_DT + 24;
     // ---- working vectors behind the image --------------------------------------------------------------------------
-    static constexpr int V_RHS = IMG, V_XT = V_RHS + NV, V_W = V_XT + NV, V_PARTF = V_W + NV, V_RB = V_PARTF + 296;
+    static constexpr int V_RHS = IMG, V_XT = V_RHS + NV, V_W = V_XT + NV, V_PPV = V_W + NV, V_PARTF = V_PPV + 416, V_RB = V_PARTF + 472;
     static constexpr int V_PSUM = V_RB + 72, V_SC = V_PSUM + 64, V_UMAX = V_SC + 8, V_ISC = V_UMAX + UM_COUNT;
+    static constexpr int PTID = 416;                   // thread that owns the variable p (lane 0 of warp 13)
     static constexpr int TOTAL = V_ISC + 8;
     static constexpr size_t BYTES = (size_t)TOTAL * 8;
     // ---- global QP block ---------------------------------------------------------------------------------------------
@@ -54,16 +57,16 @@ struct AL {
     static constexpr int QPBLOCK = G_RES + R_INFO + 4;
 
     MPCB_HD static int fld(int s) { return s == 0 ? 63 : (s == 5 ? 71 : 49); }                  // leading dimension of F_s
-    MPCB_HD static int foff(int s) { return s == 0 ? 0 : 15 * 63 + (s - 1) * 29 * 49; }
-    MPCB_HD static int vidx(int k, int comp) { const int s = k / 3 > 5 ? 5 : k / 3; return 64 * s + 21 * (k - 3 * s) + comp; }
-    MPCB_HD static int sepidx(int b) { return b < 70 ? 64 * (b / 14 + 1) + b % 14 : IP; }
-    MPCB_HD static int ibase(int s) { return s == 0 ? 0 : 64 * s + 14; }                        // first interior index of segment s
+    MPCB_HD static int foff(int s) { return s == 0 ? 0 : 15 * 63 + (s - 1) * FMID; }
+    MPCB_HD static int vidx(int k, int comp) { const int s = k / 3 > 5 ? 5 : k / 3; return SEG * s + 21 * (k - 3 * s) + comp; }
+    MPCB_HD static int sepidx(int b) { return b < 70 ? SEG * (b / 14 + 1) + b % 14 : IP; }
+    MPCB_HD static int ibase(int s) { return s == 0 ? 0 : SEG * s + 14; }                        // first interior index of segment s
     // decode a padded-node-order index: false for pads
     MPCB_HD static bool decode(int i, int& k, int& comp) {
         if (i == IP) { k = -1; comp = 0; return true; }
         if (i > IP) return false;
-        const int s = (i >> 6) > 5 ? 5 : (i >> 6), rem = i - 64 * s;
-        if (s < 5 && rem == 63) return false;
+        const int s = (i / SEG) > 5 ? 5 : (i / SEG), rem = i - SEG * s;
+        if (s < 5 && rem >= 63) return false;
         const int j = rem / 21;
         k = 3 * s + j; comp = rem - 21 * j;
         return true;
@@ -71,80 +74,81 @@ struct AL {
 };
 
 // Role of a thread in the interior mat-vecs (phases B and D): which row of which W_s, and which columns it covers.
+//   segments 0 and 5: two lanes per row; lane `half` takes the 16-byte column chunks 2 q + half (q = 0, 1, ..), so the pair
+//                     reads one contiguous 32-byte piece of the vector per step
+//   middle segments : one lane per row, all 49 columns (32 from registers, 17 from shared memory)
 struct WRole {
     bool valid, paired;
     int seg, row, half;
-    int c0;          // first column of the register part (32 columns)
-    int nov;         // number of (padded) overflow columns read from shared memory, starting at column c0 + 32
     int out;         // padded-node-order index of the row
 };
 template <class SH>
 MPCB_HD WRole wrole(int tid) {
+    typedef AL<SH> L;
     WRole r;
     if (tid < 128) {
-        r.seg = 0; r.row = tid >> 1; r.half = tid & 1; r.valid = r.row < 63; r.paired = true; r.c0 = 32 * r.half; r.nov = 0; r.out = r.row;
+        r.seg = 0; r.row = tid >> 1; r.half = tid & 1; r.valid = r.row < 63; r.paired = true; r.out = r.row;
     } else if (tid < 352) {
         const int idx = tid - 128;
         r.valid = idx < 196; r.paired = false; r.half = 0;
-        r.seg = 1 + idx / 49; r.row = idx % 49; r.c0 = 0; r.nov = 18;
+        r.seg = 1 + idx / 49; r.row = idx % 49;
         if (!r.valid) { r.seg = 1; r.row = 0; }
-        r.out = 64 * r.seg + 14 + r.row;
+        r.out = L::SEG * r.seg + 14 + r.row;
     } else {
         const int idx = tid - 352;
-        r.seg = 5; r.row = idx >> 1; r.half = idx & 1; r.valid = idx < 140; r.paired = true; r.c0 = 36 * r.half; r.nov = 4;
+        r.seg = 5; r.row = idx >> 1; r.half = idx & 1; r.valid = idx < 140; r.paired = true;
         if (!r.valid) r.row = 0;
-        r.out = 334 + r.row;
+        r.out = 5 * L::SEG + 14 + r.row;
     }
     return r;
 }
-// number of real columns of row-half (seg, half): used by the exporter to zero the padding
+// column of W_seg that coefficient slot e of the thread multiplies (e < 32: registers, e >= 32: shared-memory overflow);
+// -1 for padding slots.  The exporter and the kernel share this map.
 template <class SH>
-MPCB_HD int wcols_end(const WRole& r) {
-    if (r.seg == 0) return r.half ? 63 : 32;
-    if (r.seg == 5) return r.half ? 70 : 36;
-    return 49;
+MPCB_HD int wcol(const WRole& r, int e) {
+    if (!r.valid) return -1;
+    const int col = r.paired ? 4 * (e >> 1) + 2 * r.half + (e & 1) : e;
+    return col < SH::m(r.seg) ? col : -1;
 }
 
-// Role of a thread in part = F^T rhs_I (phase B): one column of one F_s over a chunk of rows.
+// Role of a thread in part = F^T rhs_I (phase B): one column of one F_s over a chunk of at most 18 rows.
+// 468 units: segment 0 -> 4 chunks x 15 columns, middle segments -> 3 chunks x 29 columns, segment 5 -> 4 chunks x 15.
 struct FRole {
-    int unit;        // -1: none
+    int unit;        // -1: none; else index into partF = pfoff(seg) + chunk * nb(seg) + col
     int seg, col, r0, len;
 };
 template <class SH>
+MPCB_HD int pfoff(int s) { return s == 0 ? 0 : (s == 5 ? 408 : 60 + 87 * (s - 1)); }
+template <class SH>
+MPCB_HD int fchunks(int s) { return (s == 0 || s == 5) ? 4 : 3; }
+template <class SH>
 MPCB_HD FRole frole(int tid) {
+    // warps 0..11: one (middle segment, chunk) per warp, lane = column (29 of 32 lanes); warps 12..15: chunk w - 12 of
+    // segment 0 on lanes 0..14 and of segment 5 on lanes 16..30 -- every half-warp reads one F column stripe with an odd
+    // stride (conflict-free) and broadcasts its rhs chunk
     FRole f;
     f.unit = -1; f.seg = 0; f.col = 0; f.r0 = 0; f.len = 0;
-    int u = -1;
-    if (tid < 128) u = tid;
-    else if (tid >= 352) u = tid - 352 + 128;
-    else if (tid >= 324 && tid < 328) u = 288 + tid - 324;
-    if (u < 0) return f;
-    f.unit = u;
-    if (u < 232) {
-        f.seg = 1 + u / 58; const int rem = u % 58, ch = rem / 29;
-        f.col = rem % 29; f.r0 = 26 * ch; f.len = ch ? 23 : 26;
-    } else if (u < 262) {
-        const int rem = u - 232, ch = rem / 15;
-        f.seg = 0; f.col = rem % 15; f.r0 = 32 * ch; f.len = ch ? 31 : 32;
+    const int w = tid >> 5, lane = tid & 31;
+    int ch;
+    if (w < 12) {
+        if (lane >= 29) return f;
+        f.seg = 1 + w / 3; ch = w % 3; f.col = lane;
+        f.r0 = ch == 0 ? 0 : (ch == 1 ? 18 : 34); f.len = ch == 0 ? 18 : (ch == 1 ? 16 : 15);
     } else {
-        const int rem = u - 262, ch = rem / 15;
-        f.seg = 5; f.col = rem % 15; f.r0 = 36 * ch; f.len = ch ? 34 : 36;
+        if ((lane & 15) == 15) return f;
+        ch = w - 12; f.col = lane & 15;
+        if (lane < 16) { f.seg = 0; f.r0 = 16 * ch; f.len = ch == 3 ? 15 : 16; }
+        else { f.seg = 5; f.r0 = 18 * ch; f.len = ch == 3 ? 16 : 18; }
     }
+    f.unit = pfoff<SH>(f.seg) + ch * SH::nb(f.seg) + f.col;
     return f;
-}
-// unit index of (seg, col, chunk)
-template <class SH>
-MPCB_HD int funit(int s, int col, int ch) {
-    if (s == 0) return 232 + 15 * ch + col;
-    if (s == 5) return 262 + 15 * ch + col;
-    return 58 * (s - 1) + 29 * ch + col;
 }
 
 template <class SH>
 struct ACtx {
     double* sm;
     double *wovm, *wov5, *F, *C, *Jg, *hd, *ha, *pcol, *dt;
-    double *rhs, *xt, *w, *partF, *rB, *psum, *sc;
+    double *rhs, *xt, *w, *ppv, *partF, *rB, *psum, *sc;
     unsigned long long* umax;
     long long* isc;
     double* g;                     // this OCP's QP block in global memory
@@ -155,8 +159,8 @@ struct ACtx {
         sm = smem;
         wovm = sm + L::I_WOVM; wov5 = sm + L::I_WOV5; F = sm + L::I_F; C = sm + L::I_C; Jg = sm + L::I_JG; hd = sm + L::I_HD;
         ha = sm + L::I_HA; pcol = sm + L::I_PCOL; dt = sm + L::I_DT;
-        rhs = sm + L::V_RHS; xt = sm + L::V_XT; w = sm + L::V_W; partF = sm + L::V_PARTF; rB = sm + L::V_RB; psum = sm + L::V_PSUM;
-        sc = sm + L::V_SC;
+        rhs = sm + L::V_RHS; xt = sm + L::V_XT; w = sm + L::V_W; ppv = sm + L::V_PPV; partF = sm + L::V_PARTF; rB = sm + L::V_RB;
+        psum = sm + L::V_PSUM; sc = sm + L::V_SC;
         umax = reinterpret_cast<unsigned long long*>(sm + L::V_UMAX);
         isc = reinterpret_cast<long long*>(sm + L::V_ISC);
     }
@@ -168,8 +172,8 @@ struct ACtx {
 template <class SH>
 struct ATS {
     double wreg[AL<SH>::WREG];
-    double l, u, rho, zA, yA, pc;          // row role (thread r < NA)
-    double x, zB, yB, lb, ub, rhoB;        // variable role (thread i, padded node order)
+    double l, u, rho, rinv, zA, yA;        // row role (thread r < NA); rinv = 1 / rho
+    double x, zB, yB, lb, ub, rhoB, rinvB; // variable role (thread i < 404 in padded node order; p on thread PTID)
     double t, acc, acc2;                   // interior row: W rhs_I ; cross-lane exchange slots
 };
 
@@ -190,65 +194,92 @@ MPCB_DEV d2 ld2(const double* p) {          // 16-byte load (p is 16-byte aligne
     d2 r; r.a = v.x; r.b = v.y; return r;
 #endif
 }
+// variable role of a thread: padded-node-order index i (and node / component), false if the thread owns no variable
+template <class SH>
+MPCB_DEV bool vrole(int tid, int& i, int& k, int& comp) {
+    typedef AL<SH> L;
+    if (tid == L::PTID) { i = L::IP; k = -1; comp = 0; return true; }
+    if (tid >= L::IP) return false;
+    i = tid;
+    return L::decode(tid, k, comp);
+}
 
 // ---- sparse products with the constraint Jacobian A ------------------------------------------------------------------
 // (A x)_r ; x in padded node order.  Equality row r = 14 k + c (collocation at node k of segment s = k / 3):
 //     sum_l D[j,l] x_{3s+l,c} - ts pbar f_{k,c} + A[r,p] x_p        (robot_ocp.hpp:64-70 for f)
 // inequality row r = 252 + 8 k + rr: the hand-filled 8 x 22 Jacobian of node k (robot_ocp.hpp:129-160).
 template <class SH>
-MPCB_DEV double row_times(const ACtx<SH>& c, int r, double pc, const double* x) {
+MPCB_DEV double row_times(const ACtx<SH>& c, int r, const double* x) {
     typedef AL<SH> L;
     if (r < SH::NEQ) {
-        const int k = r / 14, cc = r - 14 * k, s = k / 3, j = k - 3 * s, base = 64 * s + cc;
-        double acc = c.D(j, 0) * x[base];
-        acc += c.D(j, 1) * x[base + 21];
-        acc += c.D(j, 2) * x[base + 42];
-        acc += c.D(j, 3) * x[base + 63 + (s < 5 ? 1 : 0)];
-        acc += c.mtp() * x[base + 21 * j + 7];
-        acc += pc * x[L::IP];
-        return acc;
+        const int k = r / 14, cc = r - 14 * k, s = k / 3, j = k - 3 * s, base = L::SEG * s + cc;
+        const double x0 = x[base], x1 = x[base + 21], x2 = x[base + 42], x3 = x[base + (s < 5 ? L::SEG : 63)];
+        const double xf = x[base + 21 * j + 7], xp = x[L::IP];
+        double a0 = c.D(j, 0) * x0, a1 = c.D(j, 1) * x1, a2 = c.mtp() * xf;
+        a0 += c.D(j, 2) * x2; a1 += c.D(j, 3) * x3; a2 += c.pcol[r] * xp;
+        return (a0 + a1) + a2;
     }
     const int q = r - SH::NEQ, k = q >> 3, rr = q & 7;
     const double* G = c.Jg + k * L::JGS + rr * 22;
     const double* xs = x + L::vidx(k, 0);
-    double acc = 0;
+    double a0 = 0, a1 = 0, a2 = 0, a3 = G[21] * x[L::IP];
     MPCB_UNROLL
-    for (int cc = 0; cc < 21; cc++) acc += G[cc] * xs[cc];
-    acc += G[21] * x[L::IP];
-    return acc;
+    for (int cc = 0; cc < 20; cc += 4) { a0 += G[cc] * xs[cc]; a1 += G[cc + 1] * xs[cc + 1]; a2 += G[cc + 2] * xs[cc + 2]; a3 += G[cc + 3] * xs[cc + 3]; }
+    a0 += G[20] * xs[20];
+    return (a0 + a1) + (a2 + a3);
 }
 // (A^T y)_i for variable (k, comp), i != p ; y in row order
 template <class SH>
 MPCB_DEV double col_times(const ACtx<SH>& c, int k, int comp, const double* y) {
     typedef AL<SH> L;
-    double g = 0;
+    double g0 = 0, g1 = 0, g2 = 0, g3 = 0;
     if (comp < 14) {
         const int s1 = k / 3, l1 = k - 3 * s1;
         if (k < SH::NN - 1) {
             const double* yy = y + 14 * (3 * s1) + comp;
-            g += c.D(0, l1) * yy[0]; g += c.D(1, l1) * yy[14]; g += c.D(2, l1) * yy[28];
+            g0 += c.D(0, l1) * yy[0]; g1 += c.D(1, l1) * yy[14]; g2 += c.D(2, l1) * yy[28];
         }
         if (l1 == 0 && k > 0) {
             const double* yy = y + 14 * (3 * (s1 - 1)) + comp;
-            g += c.D(0, 3) * yy[0]; g += c.D(1, 3) * yy[14]; g += c.D(2, 3) * yy[28];
+            g0 += c.D(0, 3) * yy[0]; g1 += c.D(1, 3) * yy[14]; g2 += c.D(2, 3) * yy[28];
         }
     }
-    if (comp >= 7 && k < SH::NN - 1) g += c.mtp() * y[14 * k + comp - 7];
+    if (comp >= 7 && k < SH::NN - 1) g3 += c.mtp() * y[14 * k + comp - 7];
     const double* G = c.Jg + k * L::JGS + comp;
     const double* yi = y + SH::NEQ + 8 * k;
     MPCB_UNROLL
-    for (int rr = 0; rr < 8; rr++) g += G[rr * 22] * yi[rr];
-    return g;
+    for (int rr = 0; rr < 8; rr += 4) { g0 += G[rr * 22] * yi[rr]; g1 += G[(rr + 1) * 22] * yi[rr + 1]; g2 += G[(rr + 2) * 22] * yi[rr + 2]; g3 += G[(rr + 3) * 22] * yi[rr + 3]; }
+    return (g0 + g1) + (g2 + g3);
 }
-// partial sums of (A^T y)_p = sum_r A[r,p] y_r  by the last 32 threads
+// A[r, p]: equality rows from pcol, inequality rows from the last Jacobian column
 template <class SH>
-MPCB_DEV void pcol_partial(const ACtx<SH>& c, int tid, const double* y, double* out) {
-    if (tid < NT - 32) return;
-    const int j = tid - (NT - 32);
-    double s = 0;
-    for (int r = j; r < SH::NEQ; r += 32) s += c.pcol[r] * y[r];
-    for (int r = j; r < SH::NINEQ; r += 32) s += c.Jg[(r >> 3) * AL<SH>::JGS + (r & 7) * 22 + 21] * y[SH::NEQ + r];
-    out[j] = s;
+MPCB_DEV double pcoef(const ACtx<SH>& c, int r) {
+    if (r < SH::NEQ) return c.pcol[r];
+    const int q = r - SH::NEQ;
+    return c.Jg[(q >> 3) * AL<SH>::JGS + (q & 7) * 22 + 21];
+}
+// 32 partial sums of a row-indexed vector v (length 416, zero padded) by warp 13: psum[lane] = sum_j v[lane + 32 j]
+template <class SH>
+MPCB_DEV void psum32(const ACtx<SH>& c, int tid, const double* v, double* out) {
+    if (tid < AL<SH>::PTID || tid >= AL<SH>::PTID + 32) return;
+    const double* p = v + (tid - AL<SH>::PTID);
+    double a0 = p[0], a1 = p[32], a2 = p[64], a3 = p[96];
+    a0 += p[128]; a1 += p[160]; a2 += p[192]; a3 += p[224];
+    a0 += p[256]; a1 += p[288]; a2 += p[320]; a3 += p[352];
+    a0 += p[384];
+    out[tid - AL<SH>::PTID] = (a0 + a1) + (a2 + a3);
+}
+// sum of 32 values, pairwise tree
+MPCB_DEV double tree32(const double* p) {
+    double s[16];
+    MPCB_UNROLL
+    for (int i = 0; i < 16; i++) s[i] = p[2 * i] + p[2 * i + 1];
+    MPCB_UNROLL
+    for (int n = 8; n >= 1; n >>= 1) {
+        MPCB_UNROLL
+        for (int i = 0; i < n; i++) s[i] = s[2 * i] + s[2 * i + 1];
+    }
+    return s[0];
 }
 
 // ---- load ------------------------------------------------------------------------------------------------------------
@@ -259,31 +290,36 @@ MPCB_DEV void a_load(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     MPCB_UNROLL
     for (int e = 0; e < L::WREG; e++) ts.wreg[e] = g[L::G_WREG + e * NT + tid];
     for (int e = 2 * tid; e < L::IMG; e += 2 * NT) { c.sm[e] = g[L::G_IMG + e]; c.sm[e + 1] = g[L::G_IMG + e + 1]; }
-    ts.l = ts.u = ts.rho = ts.pc = 0; ts.lb = ts.ub = ts.rhoB = 0;
-    if (tid < L::NV) {
-        ts.l = g[L::G_ROW + tid]; ts.u = g[L::G_ROW + L::NV + tid]; ts.rho = g[L::G_ROW + 2 * L::NV + tid]; ts.pc = g[L::G_ROW + 3 * L::NV + tid];
-        ts.lb = g[L::G_VAR + tid]; ts.ub = g[L::G_VAR + L::NV + tid]; ts.rhoB = g[L::G_VAR + 2 * L::NV + tid];
-        c.rhs[tid] = 0; c.xt[tid] = 0; c.w[tid] = 0;
+    ts.l = ts.u = 0; ts.rho = ts.rinv = 1; ts.lb = ts.ub = 0; ts.rhoB = ts.rinvB = 1;
+    if (tid < SH::NA) {
+        ts.l = g[L::G_ROW + tid]; ts.u = g[L::G_ROW + L::NV + tid]; ts.rho = g[L::G_ROW + 2 * L::NV + tid];
+        ts.rinv = 1.0 / ts.rho;
     }
+    int i, k, comp;
+    if (vrole<SH>(tid, i, k, comp)) {
+        ts.lb = g[L::G_VAR + i]; ts.ub = g[L::G_VAR + L::NV + i]; ts.rhoB = g[L::G_VAR + 2 * L::NV + i];
+        ts.rinvB = 1.0 / ts.rhoB;
+    }
+    if (tid < L::NV) { c.rhs[tid] = 0; c.xt[tid] = 0; c.w[tid] = 0; }
+    if (tid < 416) c.ppv[tid] = 0;
     ts.zA = ts.yA = ts.x = ts.zB = ts.yB = ts.t = ts.acc = ts.acc2 = 0;     // boxADMM starts cold (warm_start = false)
     if (tid < 72) c.rB[tid] = 0;
-    if (tid < 296) c.partF[tid] = 0;
+    if (tid < 472) c.partF[tid] = 0;
     if (tid < 64) c.psum[tid] = 0;
     if (tid < UM_COUNT) c.umax[tid] = 0;
     if (tid == 0) { c.isc[IS_QP_DONE] = 0; c.isc[IS_QP_STATUS] = 2; c.isc[IS_QP_ITERS] = 0; }
 }
 
-// ---- phase A: rhs ------------------------------------------------------------------------------------------------------
+// ---- phase A: rhs = sigma x - h + rho_b z_b - y_b + A^T w ;  warp 13 folds the products A[r,p] w_r into 32 partial sums ----
 template <class SH>
 MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid) {
-    typedef AL<SH> L;
-    int k, comp;
-    if (tid <= L::IP && L::decode(tid, k, comp)) {
-        const double g = (k >= 0) ? col_times(c, k, comp, c.w) : 0.0;
+    int i, k, comp;
+    if (vrole<SH>(tid, i, k, comp)) {
+        const double g = (k >= 0) ? col_times(c, k, comp, c.w) : 0.0;     // p: the gather arrives through psum in phase B'
         const double h = (k < 0) ? 1.0 : 0.0;              // gradient of the Mayer cost p (robot_ocp.hpp:206)
-        c.rhs[tid] = c.st->qp_sigma * ts.x - h + ts.rhoB * ts.zB - ts.yB + g;
+        c.rhs[i] = c.st->qp_sigma * ts.x - h + ts.rhoB * ts.zB - ts.yB + g;
     }
-    pcol_partial(c, tid, c.w, c.psum);
+    psum32(c, tid, c.ppv, c.psum);
 }
 
 // ---- phase B: t = W rhs_I (register-resident rows) and part = F^T rhs_I ----------------------------------------------
@@ -291,48 +327,51 @@ template <class SH>
 MPCB_DEV void b_interior(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
     const WRole r = wrole<SH>(tid);
-    {
-        const double* b = c.rhs + L::ibase(r.seg) + r.c0;
-        double a0 = 0, a1 = 0;
-        MPCB_UNROLL
-        for (int e = 0; e < L::WREG; e += 2) {
-            const d2 v = ld2(b + e);
-            a0 += ts.wreg[e] * v.a; a1 += ts.wreg[e + 1] * v.b;
-        }
-        if (r.nov == 18) {
-            const double* wo = c.wovm + (tid - 128);
-            MPCB_UNROLL
-            for (int e = 0; e < 18; e += 2) {
-                const d2 v = ld2(b + 32 + e);
-                a0 += wo[e * 224] * v.a; a1 += wo[(e + 1) * 224] * v.b;
-            }
-        } else if (r.nov == 4) {
-            const double* wo = c.wov5 + (tid - 352);
-            MPCB_UNROLL
-            for (int e = 0; e < 4; e += 2) {
-                const d2 v = ld2(b + 32 + e);
-                a0 += wo[e * 160] * v.a; a1 += wo[(e + 1) * 160] * v.b;
-            }
-        }
-        ts.acc = a0 + a1;
-    }
     const FRole f = frole<SH>(tid);
+    if (r.paired) {
+        const double* b = c.rhs + L::ibase(r.seg) + 2 * r.half;
+        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        MPCB_UNROLL
+        for (int q = 0; q < 16; q += 2) {
+            const d2 v = ld2(b + 4 * q), v2 = ld2(b + 4 * q + 4);
+            a0 += ts.wreg[2 * q] * v.a; a1 += ts.wreg[2 * q + 1] * v.b; a2 += ts.wreg[2 * q + 2] * v2.a; a3 += ts.wreg[2 * q + 3] * v2.b;
+        }
+        if (r.seg == 5) {
+            const double* wo = c.wov5 + (tid - 352);
+            const d2 v = ld2(b + 64), v2 = ld2(b + 68);
+            a0 += wo[0] * v.a; a1 += wo[160] * v.b; a2 += wo[320] * v2.a; a3 += wo[480] * v2.b;
+        }
+        ts.acc = (a0 + a1) + (a2 + a3);
+    } else {
+        const double* b = c.rhs + L::ibase(r.seg);
+        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        MPCB_UNROLL
+        for (int e = 0; e < L::WREG; e += 4) {
+            const d2 v = ld2(b + e), v2 = ld2(b + e + 2);
+            a0 += ts.wreg[e] * v.a; a1 += ts.wreg[e + 1] * v.b; a2 += ts.wreg[e + 2] * v2.a; a3 += ts.wreg[e + 3] * v2.b;
+        }
+        const double* wo = c.wovm + (tid - 128);
+        MPCB_UNROLL
+        for (int e = 0; e < 16; e += 4) {
+            const d2 v = ld2(b + 32 + e), v2 = ld2(b + 34 + e);
+            a0 += wo[e * 224] * v.a; a1 += wo[(e + 1) * 224] * v.b; a2 += wo[(e + 2) * 224] * v2.a; a3 += wo[(e + 3) * 224] * v2.b;
+        }
+        const d2 v = ld2(b + 48);
+        a0 += wo[16 * 224] * v.a; a1 += wo[17 * 224] * v.b;
+        ts.acc = (a0 + a1) + (a2 + a3);
+    }
     if (f.unit >= 0) {
         const double* Fc = c.F + L::foff(f.seg) + f.col * L::fld(f.seg) + f.r0;
         const double* b = c.rhs + L::ibase(f.seg) + f.r0;
-        double a0 = 0, a1 = 0;
-        int i = 0;
-        for (; i + 1 < f.len; i += 2) {
-            const d2 v = ld2(b + i);
-            a0 += Fc[i] * v.a; a1 += Fc[i + 1] * v.b;
+        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        MPCB_UNROLL
+        for (int i = 0; i < 16; i += 4) {       // every chunk has at least 15 rows
+            const d2 v = ld2(b + i), v2 = ld2(b + i + 2);
+            a0 += Fc[i] * v.a; a1 += Fc[i + 1] * v.b; a2 += Fc[i + 2] * v2.a;
+            if (i + 3 < f.len) a3 += Fc[i + 3] * v2.b;
         }
-        if (i < f.len) a0 += Fc[i] * b[i];
-        c.partF[f.unit] = a0 + a1;
-    }
-    if (tid == NT - 1) {
-        double s = 0;
-        for (int j = 0; j < 32; j++) s += c.psum[j];
-        c.rhs[L::IP] += s;
+        if (f.len > 16) { const d2 v = ld2(b + 16); a0 += Fc[16] * v.a; a1 += Fc[17] * v.b; }
+        c.partF[f.unit] = (a0 + a1) + (a2 + a3);
     }
 }
 // ---- phase B': separator right-hand side r_B = rhs_B - sum_s (F_s^T rhs_I) -------------------------------------------
@@ -340,28 +379,46 @@ template <class SH>
 MPCB_DEV void b_seprhs(ACtx<SH>& c, int tid) {
     typedef AL<SH> L;
     if (tid >= SH::NB) return;
-    double r = c.rhs[L::sepidx(tid)];
     if (tid == SH::NB - 1) {
-        for (int s = 0; s < SH::NS; s++) { const int col = SH::nb(s) - 1; r -= c.partF[funit<SH>(s, col, 0)]; r -= c.partF[funit<SH>(s, col, 1)]; }
-    } else {
-        const int sj = tid / 14 + 1, cc = tid % 14;     // junction x_{3 sj}: right boundary of segment sj-1, left boundary of sj
-        const int cprev = (sj - 1 > 0 ? 14 : 0) + cc;
-        r -= c.partF[funit<SH>(sj - 1, cprev, 0)]; r -= c.partF[funit<SH>(sj - 1, cprev, 1)];
-        r -= c.partF[funit<SH>(sj, cc, 0)]; r -= c.partF[funit<SH>(sj, cc, 1)];
+        // p: gather of A[:,p]^T w (32 partial sums of phase A) and the last boundary column of every segment
+        double r = c.rhs[L::IP] + tree32(c.psum);
+        double q[6];
+        MPCB_UNROLL
+        for (int s = 0; s < SH::NS; s++) {
+            const double* pf = c.partF + pfoff<SH>(s) + (SH::nb(s) - 1);
+            const int nb = SH::nb(s);
+            double v = pf[0] + pf[nb];
+            v += (s == 0 || s == 5) ? (pf[2 * nb] + pf[3 * nb]) : pf[2 * nb];
+            q[s] = v;
+        }
+        r -= ((q[0] + q[1]) + (q[2] + q[3])) + (q[4] + q[5]);
+        c.rB[tid] = r;
+        return;
     }
-    c.rB[tid] = r;
+    const int sj = tid / 14 + 1, cc = tid - 14 * (sj - 1);     // junction x_{3 sj}: right boundary of segment sj-1, left of sj
+    const int sp = sj - 1, nbp = SH::nb(sp), nbo = SH::nb(sj);
+    const double* pp = c.partF + pfoff<SH>(sp) + (sp > 0 ? 14 : 0) + cc;
+    const double* po = c.partF + pfoff<SH>(sj) + cc;
+    double a = pp[0] + pp[nbp], b = po[0] + po[nbo];
+    a += (sp == 0) ? (pp[2 * nbp] + pp[3 * nbp]) : pp[2 * nbp];
+    b += (sj == 5) ? (po[2 * nbo] + po[3 * nbo]) : po[2 * nbo];
+    c.rB[tid] = c.rhs[L::sepidx(tid)] - (a + b);
 }
 // ---- phase C: x~_B = C^-1 r_B, 4 lanes per row ------------------------------------------------------------------------
 template <class SH>
 MPCB_DEV void c_separator(ACtx<SH>& c, ATS<SH>& ts, int tid) {
-    double a0 = 0, a1 = 0;
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
     if (tid < 4 * SH::NB) {
         const double* Cr = c.C + tid;
         const double* rb = c.rB + (tid & 3);
         MPCB_UNROLL
-        for (int jj = 0; jj < 18; jj += 2) { a0 += Cr[jj * 284] * rb[4 * jj]; a1 += Cr[(jj + 1) * 284] * rb[4 * jj + 4]; }
+        for (int jj = 0; jj < 16; jj += 4) {
+            a0 += Cr[jj * 284] * rb[4 * jj]; a1 += Cr[(jj + 1) * 284] * rb[4 * jj + 4];
+            a2 += Cr[(jj + 2) * 284] * rb[4 * jj + 8]; a3 += Cr[(jj + 3) * 284] * rb[4 * jj + 12];
+        }
+        a0 += Cr[16 * 284] * rb[64]; a1 += Cr[17 * 284] * rb[68];
     }
-    ts.acc = a0 + a1;
+    ts.acc = (a0 + a1) + (a2 + a3);
 }
 // ---- phase D: x~_I = t - F x~_B ----------------------------------------------------------------------------------------
 template <class SH>
@@ -370,48 +427,56 @@ MPCB_DEV void d_interior(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     const WRole r = wrole<SH>(tid);
     const int s = r.seg, ld = L::fld(s);
     const double* Fr = c.F + L::foff(s) + r.row;
-    double a0 = 0, a1 = 0;
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
     if (s == 0 || s == 5) {
         // 15 boundary columns: 14 junction states + p, split over the two lanes of the row (8 | 7)
-        const double* xj = c.xt + (s == 0 ? 64 : 320);
-        if (r.half == 0) {
-            MPCB_UNROLL
-            for (int cc = 0; cc < 8; cc += 2) { const d2 v = ld2(xj + cc); a0 += Fr[cc * ld] * v.a; a1 += Fr[(cc + 1) * ld] * v.b; }
-        } else {
-            MPCB_UNROLL
-            for (int cc = 8; cc < 14; cc += 2) { const d2 v = ld2(xj + cc); a0 += Fr[cc * ld] * v.a; a1 += Fr[(cc + 1) * ld] * v.b; }
-            a0 += Fr[14 * ld] * c.xt[L::IP];
-        }
+        const double* xj = c.xt + (s == 0 ? L::SEG : 5 * L::SEG) + 8 * r.half;
+        const double* Fh = Fr + 8 * r.half * ld;
+        const d2 v0 = ld2(xj), v1 = ld2(xj + 2), v2 = ld2(xj + 4);
+        a0 += Fh[0] * v0.a; a1 += Fh[ld] * v0.b; a2 += Fh[2 * ld] * v1.a; a3 += Fh[3 * ld] * v1.b;
+        a0 += Fh[4 * ld] * v2.a; a1 += Fh[5 * ld] * v2.b;
+        if (r.half == 0) { const d2 v3 = ld2(xj + 6); a2 += Fh[6 * ld] * v3.a; a3 += Fh[7 * ld] * v3.b; }
+        else a2 += Fh[6 * ld] * c.xt[L::IP];
     } else {
-        const double* x1 = c.xt + 64 * s;
-        const double* x2 = c.xt + 64 * (s + 1);
+        const double* x1 = c.xt + L::SEG * s;
+        const double* x2 = c.xt + L::SEG * (s + 1);
         MPCB_UNROLL
-        for (int cc = 0; cc < 14; cc += 2) { const d2 v = ld2(x1 + cc); a0 += Fr[cc * ld] * v.a; a1 += Fr[(cc + 1) * ld] * v.b; }
+        for (int cc = 0; cc < 12; cc += 4) {
+            const d2 v = ld2(x1 + cc), v2 = ld2(x1 + cc + 2);
+            a0 += Fr[cc * ld] * v.a; a1 += Fr[(cc + 1) * ld] * v.b; a2 += Fr[(cc + 2) * ld] * v2.a; a3 += Fr[(cc + 3) * ld] * v2.b;
+        }
+        { const d2 v = ld2(x1 + 12); a0 += Fr[12 * ld] * v.a; a1 += Fr[13 * ld] * v.b; }
         MPCB_UNROLL
-        for (int cc = 0; cc < 14; cc += 2) { const d2 v = ld2(x2 + cc); a0 += Fr[(14 + cc) * ld] * v.a; a1 += Fr[(15 + cc) * ld] * v.b; }
+        for (int cc = 0; cc < 12; cc += 4) {
+            const d2 v = ld2(x2 + cc), v2 = ld2(x2 + cc + 2);
+            a0 += Fr[(14 + cc) * ld] * v.a; a1 += Fr[(15 + cc) * ld] * v.b; a2 += Fr[(16 + cc) * ld] * v2.a; a3 += Fr[(17 + cc) * ld] * v2.b;
+        }
+        { const d2 v = ld2(x2 + 12); a2 += Fr[26 * ld] * v.a; a3 += Fr[27 * ld] * v.b; }
         a0 += Fr[28 * ld] * c.xt[L::IP];
     }
-    ts.acc = r.valid ? a0 + a1 : 0.0;
+    ts.acc = r.valid ? (a0 + a1) + (a2 + a3) : 0.0;
 }
 // ---- phase E: rows and variables update --------------------------------------------------------------------
+// y/rho is evaluated as y * (1/rho) with the reciprocal taken once per QP (an FP64 division costs ~130 cycles of latency).
 template <class SH>
 MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
-    typedef AL<SH> L;
     const double al = c.st->qp_alpha;
     if (tid < SH::NA) {
-        const double ax = row_times(c, tid, ts.pc, c.xt);
+        const double ax = row_times(c, tid, c.xt);
         const double zh = al * ax + (1 - al) * ts.zA;
-        const double zn = dmin(dmax(zh + ts.yA / ts.rho, ts.l), ts.u);
+        const double zn = dmin(dmax(zh + ts.yA * ts.rinv, ts.l), ts.u);
         ts.yA += ts.rho * (zh - zn);
         ts.zA = zn;
-        c.w[tid] = ts.rho * ts.zA - ts.yA;
+        const double w = ts.rho * ts.zA - ts.yA;
+        c.w[tid] = w;
+        c.ppv[tid] = pcoef(c, tid) * w;
     }
-    int k, comp;
-    if (tid <= L::IP && L::decode(tid, k, comp)) {
-        const double xt = c.xt[tid];
+    int i, k, comp;
+    if (vrole<SH>(tid, i, k, comp)) {
+        const double xt = c.xt[i];
         ts.x = al * xt + (1 - al) * ts.x;
         const double zh = al * xt + (1 - al) * ts.zB;
-        const double zn = dmin(dmax(zh + ts.yB / ts.rhoB, ts.lb), ts.ub);
+        const double zn = dmin(dmax(zh + ts.yB * ts.rinvB, ts.lb), ts.ub);
         ts.yB += ts.rhoB * (zh - zn);
         ts.zB = zn;
     }
@@ -420,31 +485,32 @@ MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 template <class SH>
 MPCB_DEV void chk_a(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
-    if (tid < SH::NA) c.rhs[tid] = ts.yA;       // the rhs slot is free until the next phase A
-    int k, comp;
-    if (tid <= L::IP && L::decode(tid, k, comp)) c.xt[tid] = ts.x;
+    if (tid < SH::NA) { c.rhs[tid] = ts.yA; c.partF[tid] = pcoef(c, tid) * ts.yA; }      // rhs / partF are free until the next phase A / B
+    else if (tid < 416) c.partF[tid] = 0;
+    int i, k, comp;
+    if (vrole<SH>(tid, i, k, comp)) c.xt[i] = ts.x;
 }
 template <class SH>
 MPCB_DEV void chk_b(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
     double rp = 0, nax = 0, nz = 0, nx = 0, rd = 0, nhx = 0, naty = 0;
     if (tid < SH::NA) {
-        const double ax = row_times(c, tid, ts.pc, c.xt);
+        const double ax = row_times(c, tid, c.xt);
         rp = fabs(ax - ts.zA); nax = fabs(ax); nz = fabs(ts.zA);
     }
-    int k, comp;
-    if (tid <= L::IP && L::decode(tid, k, comp)) {
+    int i, k, comp;
+    if (vrole<SH>(tid, i, k, comp)) {
         nx = fabs(ts.x); nz = dmax(nz, fabs(ts.zB)); rp = dmax(rp, fabs(ts.x - ts.zB));
         if (k >= 0) {
             const double aty = col_times(c, k, comp, c.rhs) + ts.yB;
-            const double hx = c.hd[tid] * ts.x + c.ha[tid] * c.xt[L::IP];
+            const double hx = c.hd[i] * ts.x + c.ha[i] * c.xt[L::IP];
             naty = fabs(aty); nhx = fabs(hx); rd = fabs(hx + aty);
         }
     }
-    pcol_partial(c, tid, c.rhs, c.psum);
+    psum32(c, tid, c.partF, c.psum);                    // (A^T y)_p
     if (tid >= NT - 32) {
         double s = 0;
-        for (int i = tid - (NT - 32); i < L::IP; i += 32) s += c.ha[i] * c.xt[i];     // pads hold zeros
+        for (int j = tid - (NT - 32); j < L::IP; j += 32) s += c.ha[j] * c.xt[j];     // H[p,.] x ; pads hold zeros
         c.psum[32 + tid - (NT - 32)] = s;
     }
     umax_accum(c.umax + UM_RP, rp); umax_accum(c.umax + UM_NAX, nax); umax_accum(c.umax + UM_NZ, nz); umax_accum(c.umax + UM_NX, nx);
@@ -453,9 +519,8 @@ MPCB_DEV void chk_b(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 template <class SH>
 MPCB_DEV void chk_c(ACtx<SH>& c, ATS<SH>& ts, int tid, int iter) {
     typedef AL<SH> L;
-    if (tid != L::IP) return;
-    double s1 = 0, s2 = 0;
-    for (int j = 0; j < 32; j++) { s1 += c.psum[j]; s2 += c.psum[32 + j]; }
+    if (tid != L::PTID) return;
+    const double s1 = tree32(c.psum), s2 = tree32(c.psum + 32);
     const double aty = s1 + ts.yB, hx = c.hd[L::IP] * ts.x + s2;
     const double rd = dmax(umax_get(c.umax + UM_RD), fabs(hx + 1.0 + aty));
     const double nhx = dmax(umax_get(c.umax + UM_NHX), fabs(hx)), naty = dmax(umax_get(c.umax + UM_NATY), fabs(aty));
@@ -472,11 +537,11 @@ MPCB_DEV void a_finish(ACtx<SH>& c, ATS<SH>& ts, int tid, int max_iter) {
     typedef AL<SH> L;
     double* res = c.g + L::G_RES;
     if (tid < SH::NA) res[L::R_LAM + tid] = ts.yA;
-    int k, comp;
-    if (tid <= L::IP && L::decode(tid, k, comp)) {
-        const int i = (k < 0) ? SH::IP : SH::kvar(k, comp);
-        res[i] = ts.x;
-        res[L::R_LAM + SH::NA + i] = ts.yB;
+    int i, k, comp;
+    if (vrole<SH>(tid, i, k, comp)) {
+        const int io = (k < 0) ? SH::IP : SH::kvar(k, comp);
+        res[io] = ts.x;
+        res[L::R_LAM + SH::NA + io] = ts.yB;
     }
     if (tid == 0) {
         res[L::R_INFO] = (double)c.isc[IS_QP_STATUS];

@@ -21,22 +21,21 @@ template <class SH>
 MPCB_DEV void exp_w(const Ctx<SH>& c, int tid, double* qb) {
     typedef AL<SH> L;
     const WRole r = wrole<SH>(tid);
-    const int cend = wcols_end<SH>(r);
     const double* Wn = c.W + SH::woff(r.seg);
     for (int e = 0; e < L::WREG; e++) {
-        const int col = r.c0 + e;
-        qb[L::G_WREG + e * NT + tid] = (r.valid && col < cend) ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
+        const int col = wcol<SH>(r, e);
+        qb[L::G_WREG + e * NT + tid] = col >= 0 ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
     }
     double* img = qb + L::G_IMG;
     if (tid >= 128 && tid < 352) {
         for (int e = 0; e < 18; e++) {
-            const int col = 32 + e;
-            img[L::I_WOVM + e * 224 + (tid - 128)] = (r.valid && col < cend) ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
+            const int col = wcol<SH>(r, 32 + e);
+            img[L::I_WOVM + e * 224 + (tid - 128)] = col >= 0 ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
         }
     } else if (tid >= 352) {
         for (int e = 0; e < 4; e++) {
-            const int col = r.c0 + 32 + e;
-            img[L::I_WOV5 + e * 160 + (tid - 352)] = (r.valid && col < cend) ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
+            const int col = wcol<SH>(r, 32 + e);
+            img[L::I_WOV5 + e * 160 + (tid - 352)] = col >= 0 ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
         }
     }
 }
@@ -47,10 +46,10 @@ MPCB_DEV void exp_fc(const Ctx<SH>& c, int tid, double* qb) {
     double* img = qb + L::G_IMG;
     for (int e = tid; e < L::FSZ; e += NT) {
         double v = 0.0;
-        if (e < L::FSZ - 2) {
-            const int s = e < 945 ? 0 : (e < 6629 ? 1 + (e - 945) / 1421 : 5);
+        {
+            const int s = e < 945 ? 0 : (e < 945 + 4 * L::FMID ? 1 + (e - 945) / L::FMID : 5);
             const int off = e - L::foff(s), ld = L::fld(s), col = off / ld, i = off - col * ld;
-            if (i < SH::m(s)) v = c.F[SH::foff(s) + i * SH::nb(s) + col];
+            if (i < SH::m(s) && col < SH::nb(s)) v = c.F[SH::foff(s) + i * SH::nb(s) + col];
         }
         img[L::I_F + e] = v;
     }

@@ -30,11 +30,14 @@ body = [r for r in rows if len(r) == len(hdr) and r[0].startswith("0x")]
 base = int(body[0][0], 16)
 iS = hdr.index("# Samples"); iE = hdr.index("Instructions Executed")
 by = collections.Counter(); ex = collections.Counter(); tot = 0
+stall_cols = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
+stalls = collections.defaultdict(collections.Counter)
 for r in body:
     off = int(r[0], 16) - base
     key = line_of.get(off, ((None, 0), ""))[0]
     s = int(r[iS] or 0); tot += s
     by[key] += s; ex[key] += int(r[iE] or 0)
+    for i in stall_cols: stalls[key][hdr[i][6:]] += int(r[i] or 0)
 print(f"total samples {tot}, instructions {sum(ex.values())}")
 srccache = {}
 for key, s in by.most_common(top):
@@ -45,4 +48,5 @@ for key, s in by.most_common(top):
         if p:
             srccache.setdefault(p[0], open(p[0]).read().splitlines())
             text = srccache[p[0]][ln - 1].strip()[:100]
-    print(f"{100*s/tot:5.1f}%  inst {ex[key]:>11}  {f}:{ln}  {text}")
+    why = " ".join(f"{k}={v}" for k, v in stalls[key].most_common(3) if v)
+    print(f"{100*s/tot:5.1f}%  inst {ex[key]:>11}  {f}:{ln}  {text[:70]}  | {why}")

@@ -31,3 +31,10 @@ build/prof_kernels.o: $(SRC)/mpcb_kernels.cu $(HDR)
 	$(NVCC) $(NVFLAGS) -DMPCB_PROFILE -c $< -o $@
 $(PROF_OUT): build/prof_kernels.o build/mpcb_capi.o build/mpcb_planner_host.o
 	$(NVCC) -shared -o $@ $^ -cudart shared -Xlinker -rpath=$(CUDA_HOME)/lib64
+
+# Example mains on top of include/motion_planner.hpp (ports of the reference's examples/*.cpp call sequences)
+examples: build/offline_trajectory build/mpc_benchmark
+build/offline_trajectory: examples/offline_trajectory.cpp include/motion_planner.hpp $(OUT)
+	$(CXX) -O2 -std=c++17 -Wall -Iinclude $< -o $@ -L$(dir $(OUT)) -lmpcb -Wl,-rpath,'$$ORIGIN/../$(dir $(OUT))'
+build/mpc_benchmark: examples/benchmark.cpp include/motion_planner.hpp $(OUT)
+	$(CXX) -O2 -std=c++17 -Wall -Iinclude $< -o $@ -L$(dir $(OUT)) -lmpcb -Wl,-rpath,'$$ORIGIN/../$(dir $(OUT))'

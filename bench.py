@@ -135,8 +135,10 @@ def run_ours(args):
     B = args.batch
     s = M.default_settings(); lim = M.default_limits(MARGINS)
     # rank r owns problems [r*B, (r+1)*B) of the global seed-1 batch (generator streams are indexed by problem)
+    from mpc_motion_planner_b200.sharding import shard_range
     x0a, xTa = M.generate_problems(lim, 0, 1, B * world)
-    x0 = x0a[rank * B:(rank + 1) * B].copy(); xT = xTa[rank * B:(rank + 1) * B].copy()
+    lo, hi = shard_range(rank, world, B * world)
+    x0 = x0a[lo:hi].copy(); xT = xTa[lo:hi].copy()
     gx, gu, gT = M.guess_batch(s, lim, x0, xT)
     sv = M.Solver(s, lim, device=local)
     N = sv.N
@@ -206,21 +208,16 @@ def run_ours(args):
     h2d = B * (14 + 14 + 14 * N + 7 * N + 1) * 8
     d2h = B * ((14 * N + 7 * N + 1) * 8 + M.capi.STATS_DTYPE.itemsize)
     # ---- max over ranks + statistics gather ---------------------------------------------------------------------------
-    loc = torch.tensor([ms_total, t_e2e, flops_step, float((stats["status"] == 1).sum()), float(stats["qp_iters_total"].sum()),
-                        float(stats["sqp_iters"].sum()), float(sol_T.sum()), float(sol_T.min()), float(sol_T.max()), float(B)],
-                       dtype=torch.float64, device=dev)
-    if dist is not None:
-        allr = [torch.empty_like(loc) for _ in range(world)]
-        dist.all_gather(allr, loc)
-        allr = torch.stack(allr).cpu().numpy()
-    else:
-        allr = loc.cpu().numpy()[None]
+    from mpc_motion_planner_b200 import sharding
+    loc = sharding.local_stats(ms_total, t_e2e, flops_step, stats["status"], stats["qp_iters_total"], stats["sqp_iters"], sol_T)
+    allr = sharding.gather_stats(loc, dist, dev)                     # the only collective of the path: per-rank statistics
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
         return
-    ms_total_max = float(allr[:, 0].max()); t_e2e_max = float(allr[:, 1].max())
-    total_ocps = float(allr[:, 9].sum())
+    red = sharding.reduce_stats(allr)
+    ms_total_max = red["ms_total_max"]; t_e2e_max = red["e2e_s_max"]
+    total_ocps = red["n_ocp"]
     ms_per_step = ms_total_max / args.steps
     value = total_ocps / (ms_per_step * 1e-3)
     fp64_peak = sv.fp64_tflops()
@@ -251,8 +248,8 @@ def run_ours(args):
                               "admm_ms": sum(admm_ms) / args.steps, "sqp_stage_ms": sum(stage_ms) / args.steps},
                      "hbm": {"achieved_gbs": algo_bytes / (ms_total / args.steps * 1e-3) / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
                              "note": "algorithmic HBM bytes per launch = inputs + outputs; the path is not HBM-bound"}},
-        "stats": {"solved": int(allr[:, 3].sum()), "admm_iters_per_ocp": float(allr[:, 4].sum() / total_ocps), "sqp_iters_per_ocp": float(allr[:, 5].sum() / total_ocps),
-                  "mean_T": float(allr[:, 6].sum() / total_ocps), "min_T": float(allr[:, 7].min()), "max_T": float(allr[:, 8].max()),
+        "stats": {"solved": red["solved"], "admm_iters_per_ocp": red["qp_iters"] / total_ocps, "sqp_iters_per_ocp": red["sqp_iters"] / total_ocps,
+                  "mean_T": red["mean_T"], "min_T": red["min_T"], "max_T": red["max_T"],
                   "wall_s_timed_region": t_wall, "p50_step_ms": float(sorted(ms_steps)[len(ms_steps) // 2])},
     }
     # single-solve latency (n = 1), device-resident

@@ -163,6 +163,18 @@ int mpcb_generate_problems(const mpcb_limits* lim, int kind, unsigned long long 
 int mpcb_guess_batch(const mpcb_settings* s, const mpcb_limits* lim, int n, const double* x0, const double* xT,
                      double* guess_x, double* guess_u, double* guess_T);
 
+/* Single-state host helpers used by the C++ MotionPlanner mirror (include/motion_planner.hpp):
+ *   mpcb_sample_random_state  MotionPlanner::sample_random_state (motionPlanner.cpp:102-114), counter-based RNG (seed, stream)
+ *   mpcb_forward_velocities   PandaWrapper::forward_velocities (robot_utils/pandaWrapper.cpp:90-107): tool twist [lin; ang]
+ *   mpcb_inverse_velocities   PandaWrapper::inverse_velocities (pandaWrapper.cpp:60-88): damped pseudo-inverse, damping 1e-5
+ *   mpcb_rnea                 pinocchio::rnea on the Panda model (motionPlanner.hpp:91-94,110-113,127)
+ *   mpcb_frame_height         z of joint 7 (frame 0; motionPlanner.cpp:111) or of panda_tool (frame 1; robot_ocp.hpp:91) */
+int mpcb_sample_random_state(const mpcb_limits* lim, unsigned long long seed, unsigned long long stream, double* q, double* v);
+int mpcb_forward_velocities(const double* q, const double* qd, double* task6);
+int mpcb_inverse_velocities(const double* q, const double* linear3, const double* angular3, double* qd);
+int mpcb_rnea(const double* q, const double* v, const double* a, double* tau);
+int mpcb_frame_height(const double* q, int frame, double* z);
+
 #ifdef __cplusplus
 }
 #endif

@@ -134,6 +134,40 @@ int mpcb_generate_problems(const mpcb_limits* lim, int kind, unsigned long long 
     return MPCB_OK;
 }
 
+// ---- single-state helpers for the MotionPlanner mirror (include/motion_planner.hpp) -----------------------------------
+int mpcb_sample_random_state(const mpcb_limits* lim, unsigned long long seed, unsigned long long stream, double* q, double* v) {
+    if (!lim || !q || !v) return MPCB_ERR_BAD_ARG;
+    Rng rng(seed, stream);
+    sample_random_state(lim, rng, q, v);
+    return MPCB_OK;
+}
+int mpcb_forward_velocities(const double* q, const double* qd, double* task6) {
+    if (!q || !qd || !task6) return MPCB_ERR_BAD_ARG;
+    forward_velocities(q, qd, task6);
+    return MPCB_OK;
+}
+int mpcb_inverse_velocities(const double* q, const double* linear3, const double* angular3, double* qd) {
+    if (!q || !linear3 || !angular3 || !qd) return MPCB_ERR_BAD_ARG;
+    const double task[6] = {linear3[0], linear3[1], linear3[2], angular3[0], angular3[1], angular3[2]};
+    inverse_velocities(q, task, qd);
+    return MPCB_OK;
+}
+int mpcb_rnea(const double* q, const double* v, const double* a, double* tau) {
+    if (!q || !v || !a || !tau) return MPCB_ERR_BAD_ARG;
+    double g[8];
+    rbd::node_constraints_value(q, v, a, g);
+    for (int j = 0; j < 7; j++) tau[j] = g[j];
+    return MPCB_OK;
+}
+int mpcb_frame_height(const double* q, int frame, double* z) {
+    if (!q || !z || frame < 0 || frame > 1) return MPCB_ERR_BAD_ARG;
+    const double zero[3] = {0, 0, 0};
+    double pos[3];
+    rbd::fk_point7(q, frame == 0 ? zero : PANDA(PANDA_TOOL_OFFSET), pos);
+    *z = pos[2];
+    return MPCB_OK;
+}
+
 int mpcb_num_nodes(const mpcb_settings* s) { return s->poly_order * s->num_seg + 1; }
 int mpcb_num_var(const mpcb_settings* s) { return 21 * mpcb_num_nodes(s) + 1; }
 int mpcb_num_dual(const mpcb_settings* s) { const int n = mpcb_num_nodes(s); return 14 * (n - 1) + 8 * n + 21 * n + 1; }

@@ -1,0 +1,63 @@
+"""The C++ MotionPlanner mirror (include/motion_planner.hpp) and the ported example mains (examples/*.cpp)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _build():
+    subprocess.check_call(["make", "-s", "-C", ROOT, "examples"])
+    return os.path.join(ROOT, "build", "offline_trajectory"), os.path.join(ROOT, "build", "mpc_benchmark")
+
+
+def test_examples_build_and_fail_loudly_without_a_gpu():
+    import torch
+    off, _ = _build()
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu tests")
+    r = subprocess.run([off, "/tmp/should_not_exist.txt"], capture_output=True, text=True)
+    assert r.returncode != 0 and "no CUDA device" in (r.stderr + r.stdout)
+    assert not os.path.exists("/tmp/should_not_exist.txt")
+
+
+@pytest.mark.gpu
+def test_offline_trajectory_file_format(tmp_path):
+    off, _ = _build()
+    out = tmp_path / "optimal_solution.txt"
+    r = subprocess.run([off, str(out), "5"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    a = np.loadtxt(out)
+    assert a.shape == (403, 29)                      # offline_trajectory.cpp:69-105, data_analysis.ipynb cell 4
+    rk, mpc = a[1:202], a[202:]
+    assert rk[0, 0] == 0 and mpc[0, 0] == 0 and np.all(np.diff(mpc[:, 0]) > 0)
+    assert np.abs(mpc[-1, 1:15] - a[0, 1:15]).max() <= 1e-2 + 1e-4     # final state inside the +-eps box (file has 6 digits)
+    assert np.abs(rk[0, 1:15] - mpc[0, 1:15]).max() < 1e-5             # both start at the pinned initial state
+    T_rk, T_mpc = rk[-1, 0], mpc[-1, 0]
+    assert 0 < T_mpc <= 10 and 0 < T_rk <= 10
+
+
+@pytest.mark.gpu
+def test_mpc_benchmark_rows(tmp_path):
+    _, ben = _build()
+    out = tmp_path / "benchmark_data.txt"
+    r = subprocess.run([ben, "64", str(out), "1"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    a = np.loadtxt(out)
+    assert a.shape == (64, 162)                      # benchmark.cpp:164-194
+    flags = a[:, 140:148]
+    assert set(np.unique(flags)) <= {0.0, 1.0}
+    assert np.all(a[:, 56:84] <= a[:, 84:112] + 1e-12)              # MPC minima <= maxima
+    # the same problems through the Python binding give the same final-state errors (6 printed digits)
+    import mpc_motion_planner_b200 as M
+    lim = M.default_limits([0.8, 0.8, 0.6, 0.9, 0.1]); s = M.default_settings()
+    x0, xT = M.generate_problems(lim, 0, 1, 64)
+    assert np.abs(a[:, 148:162] - xT).max() < 1e-5
+    gx, gu, gT = M.guess_batch(s, lim, x0, xT)
+    sv = M.Solver(s, lim, device=0)
+    sx, su, sT, _, st = sv.solve(x0, xT, gx, gu, gT)
+    _, acc = sv.sample(sx, su, sT, target=xT, npts=200, want_traj=False)
+    assert np.abs(a[:, 126:140] - acc["final_err"]).max() < 1e-5
+    sv.close()

@@ -164,7 +164,7 @@ def run_ours(args):
     barrier()
     launches0 = sv.launch_count()
     evs = []
-    admm_ms = []; stage_ms = []; admm_launches = 0
+    admm_ms = []; stage_ms = []; node_ms = []; admm_launches = 0
     with ClockSampler(local) as clk:
         t_wall0 = time.perf_counter()
         for _ in range(args.steps):
@@ -172,7 +172,7 @@ def run_ours(args):
             a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
             a.record(); step_device(); b.record()
             evs.append((a, b))
-            admm_ms.append(sv.last_kernel_ms(1)); stage_ms.append(sv.last_kernel_ms(0))      # per-launch CUDA events on the launch stream
+            admm_ms.append(sv.last_kernel_ms(1)); stage_ms.append(sv.last_kernel_ms(0)); node_ms.append(sv.last_kernel_ms(2))   # per-launch CUDA events
             admm_launches += sv.last_kernel_launches(1)
         barrier()
         t_wall = time.perf_counter() - t_wall0
@@ -245,7 +245,7 @@ def run_ours(args):
                      "kernel": "admm_kernel", "flops_per_launch": flops_admm_launch, "kernel_ms": admm_ms_launch,
                      "kernel_share_of_step": sum(admm_ms) / ms_total,
                      "step": {"flops": flops_step, "ms": ms_total / args.steps, "achieved": achieved_step,
-                              "admm_ms": sum(admm_ms) / args.steps, "sqp_stage_ms": sum(stage_ms) / args.steps},
+                              "admm_ms": sum(admm_ms) / args.steps, "sqp_stage_ms": sum(stage_ms) / args.steps, "node_ms": sum(node_ms) / args.steps},
                      "hbm": {"achieved_gbs": algo_bytes / (ms_total / args.steps * 1e-3) / 1e9, "peak_gbs": peaks.get("hbm_gbs"),
                              "note": "algorithmic HBM bytes per launch = inputs + outputs; the path is not HBM-bound"}},
         "stats": {"solved": red["solved"], "admm_iters_per_ocp": red["qp_iters"] / total_ocps, "sqp_iters_per_ocp": red["sqp_iters"] / total_ocps,

@@ -135,14 +135,16 @@ double mpcb_last_solve_ms(mpcb_handle* h);
 /* Number of kernel launches issued by this handle so far. */
 long long mpcb_launch_count(const mpcb_handle* h);
 /* The last mpcb_solve_batch split by kernel kind: 0 = SQP stage kernels (linearise, factorise, line search, step),
- * 1 = ADMM kernel (the QP iterations).  Summed device time in ms (CUDA events around each launch) and launch count. */
-enum { MPCB_KERNEL_SQP_STAGE = 0, MPCB_KERNEL_ADMM = 1 };
+ * 1 = ADMM kernel (the QP iterations), 2 = node kernels (RNEA values / derivatives, one thread per node of the batch).
+ * Summed device time in ms (CUDA events around each launch) and launch count. */
+enum { MPCB_KERNEL_SQP_STAGE = 0, MPCB_KERNEL_ADMM = 1, MPCB_KERNEL_NODE = 2 };
 double mpcb_last_kernel_ms(mpcb_handle* h, int kind);
 int mpcb_last_kernel_launches(const mpcb_handle* h, int kind);
 /* Debug: cumulative SM cycles per ADMM phase of CTA 0 (all zero unless libmpcb was built with -DMPCB_PROFILE).
- * Slots: 0 load, 1 rhs, 2 interior W/F^T, 3 separator rhs, 4 separator solve, 5 interior back-substitution, 6 row/box
- * update, 7 residual test, 8 store. */
-int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out16, int reset);
+ * ADMM kernel slots: 0 load, 1 rhs, 2 interior W/F^T, 3 separator rhs, 4 separator solve, 5 interior back-substitution,
+ * 6 row/box update, 7 residual test, 8 store.  SQP stage slots: 16 load, 17 linearise, 18 KKT assembly, 19 interior sweeps,
+ * 20 separator, 21 export, 22 merit + line search, 23 step + termination, 24 store, 25 factorise tail. */
+int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out32, int reset);
 
 /* FP64 FMA peak micro-benchmark on the handle's device (roofline denominator); returns TFLOP/s. */
 double mpcb_measure_fp64_tflops(mpcb_handle* h);

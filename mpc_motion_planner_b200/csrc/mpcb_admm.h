@@ -549,20 +549,6 @@ MPCB_DEV void a_finish(ACtx<SH>& c, ATS<SH>& ts, int tid, int max_iter) {
     }
 }
 
-// Per-phase cycle accounting (debug builds with -DMPCB_PROFILE only): thread 0 of CTA 0 accumulates clock64 deltas.
-#if defined(MPCB_PROFILE) && !defined(MPCB_EMUL)
-#define MPCB_PROF_DECL long long prof_last = clock64();
-#define MPCB_PROF(slot)                                                  \
-    if (tid == 0 && blockIdx.x == 0 && c.prof) {                         \
-        const long long now_ = clock64();                                \
-        c.prof[slot] += now_ - prof_last;                                \
-        prof_last = now_;                                                \
-    }
-#else
-#define MPCB_PROF_DECL
-#define MPCB_PROF(slot)
-#endif
-
 // One QP: load the block, iterate, store the result.
 template <class SH>
 MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {

@@ -93,7 +93,7 @@ int mpcb_create(const mpcb_settings* s, int device, mpcb_handle** out) {
     }
     if ((e = solve_prepare()) != cudaSuccess) return fail("cudaFuncSetAttribute(solve kernels)", e);
     h->grid_max = h->sm_count;      // one CTA per SM (shared memory bound)
-    if ((e = cudaMalloc(&h->d_prof, 16 * sizeof(long long))) != cudaSuccess || (e = cudaMemset(h->d_prof, 0, 16 * sizeof(long long))) != cudaSuccess) return fail("cudaMalloc(prof)", e);
+    if ((e = cudaMalloc(&h->d_prof, 32 * sizeof(long long))) != cudaSuccess || (e = cudaMemset(h->d_prof, 0, 32 * sizeof(long long))) != cudaSuccess) return fail("cudaMalloc(prof)", e);
     if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
     *out = h;
     return MPCB_OK;
@@ -206,10 +206,16 @@ int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, 
         bp.sx = dsx; bp.su = dsu; bp.sT = dsT; bp.slam = dsl; bp.stats = dst;
     }
     const int chunk = n < CHUNK_MAX ? n : CHUNK_MAX;
-    const int n_launch = 1 + 2 * h->st.sqp_max_iter;
+    const int n_launch = 2 + 3 * h->st.sqp_max_iter;               // persistent kernels (one work counter each) per chunk
     { int rc = ensure_workspace(h, chunk, n_launch); if (rc) return rc; }
     h->kused = 0;
     CK(cudaEventRecord(h->ev0, stream));
+#define TIMED(kind_, call_)                                                                                        \
+    do {                                                                                                           \
+        if (timed_launch_begin(h, kind_, stream)) { h->err = "cudaEventRecord failed"; return MPCB_ERR_CUDA; }     \
+        CK(call_);                                                                                                 \
+        timed_launch_end(h, stream);                                                                               \
+    } while (0)
     for (int c0 = 0; c0 < n; c0 += chunk) {
         const int nn = (n - c0) < chunk ? (n - c0) : chunk;
         const int grid = nn < h->grid_max ? nn : h->grid_max;
@@ -221,18 +227,17 @@ int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, 
         if (cp.stats) cp.stats += c0;
         CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int) * n_launch, stream));
         int li = 0;
-        if (timed_launch_begin(h, 0, stream)) { h->err = "cudaEventRecord failed"; return MPCB_ERR_CUDA; }
-        CK(launch_sqp_stage(h->kc, cp, nn, 0, grid, h->d_counter + li++, h->d_workspace, stream));
-        timed_launch_end(h, stream);
+        // load -> [node Jacobians -> linearise/factorise -> ADMM -> node trial values -> line search/step] x sqp_max_iter
+        TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 0, 0, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
         for (int it = 1; it <= h->st.sqp_max_iter; it++) {
-            if (timed_launch_begin(h, 1, stream)) { h->err = "cudaEventRecord failed"; return MPCB_ERR_CUDA; }
-            CK(launch_admm(h->kc, nn, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
-            timed_launch_end(h, stream);
-            if (timed_launch_begin(h, 0, stream)) { h->err = "cudaEventRecord failed"; return MPCB_ERR_CUDA; }
-            CK(launch_sqp_stage(h->kc, cp, nn, it, grid, h->d_counter + li++, h->d_workspace, stream));
-            timed_launch_end(h, stream);
+            TIMED(MPCB_KERNEL_NODE, launch_node_jac(nn, h->d_workspace, stream));
+            TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 1, it, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
+            TIMED(MPCB_KERNEL_ADMM, launch_admm(h->kc, nn, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
+            TIMED(MPCB_KERNEL_NODE, launch_node_val(h->kc, nn, h->d_workspace, stream));
+            TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 2, it, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
         }
     }
+#undef TIMED
     CK(cudaEventRecord(h->ev1, stream));
     h->timed = true; h->timed_stream = stream;
     if (mem == MPCB_MEM_HOST) {
@@ -312,12 +317,12 @@ double mpcb_last_kernel_ms(mpcb_handle* h, int kind) {
     }
     return total;
 }
-int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out16, int reset) {
-    if (!h || !out16) return MPCB_ERR_BAD_ARG;
+int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out32, int reset) {
+    if (!h || !out32) return MPCB_ERR_BAD_ARG;
     CK(cudaSetDevice(h->device));
     CK(cudaDeviceSynchronize());
-    CK(cudaMemcpy(out16, h->d_prof, 16 * sizeof(long long), cudaMemcpyDeviceToHost));
-    if (reset) CK(cudaMemset(h->d_prof, 0, 16 * sizeof(long long)));
+    CK(cudaMemcpy(out32, h->d_prof, 32 * sizeof(long long), cudaMemcpyDeviceToHost));
+    if (reset) CK(cudaMemset(h->d_prof, 0, 32 * sizeof(long long)));
     return MPCB_OK;
 }
 int mpcb_last_kernel_launches(const mpcb_handle* h, int kind) {

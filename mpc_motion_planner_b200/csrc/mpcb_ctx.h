@@ -48,6 +48,20 @@ constexpr int NT = 512;   // threads per CTA
 #define MPCB_PEER(field, k) __shfl_xor_sync(0xffffffffu, ts.field, k)
 #endif
 
+// Per-phase cycle accounting (debug builds with -DMPCB_PROFILE only): thread 0 of CTA 0 accumulates clock64 deltas.
+#if defined(MPCB_PROFILE) && !defined(MPCB_EMUL)
+#define MPCB_PROF_DECL long long prof_last = clock64();
+#define MPCB_PROF(slot)                                                  \
+    if (tid == 0 && blockIdx.x == 0 && c.prof) {                         \
+        const long long now_ = clock64();                                \
+        c.prof[slot] += now_ - prof_last;                                \
+        prof_last = now_;                                                \
+    }
+#else
+#define MPCB_PROF_DECL
+#define MPCB_PROF(slot)
+#endif
+
 // uniform double scalars in shared memory
 enum {
     SC_PBAR = 0,   // p at the linearisation point
@@ -99,8 +113,14 @@ struct Ctx {
     long long* isc;
     double* z;                     // global workspace: iterate, kernel order (NVAR)
     double* lam;                   // global workspace: multipliers [eq | ineq | box kernel order]
+    // global workspace filled by the node kernels (mpcb_node.h): inequality Jacobians and values at the iterate, and the
+    // inequality values at the line-search trial points  z + alpha_t p,  t = 0 (alpha = 0), 1 (alpha = 1), 2 (tau), ..
+    const double* gJg;             // NN x 176
+    const double* gGj;             // NN x 8   (values returned by the derivative pass)
+    const double* gval;            // (line_search_max_iter + 1) x NN x 8
     const mpcb_settings* st;
     const ChebConst* cheb;
+    long long* prof;               // MPCB_PROFILE builds: cycle counters of CTA 0 (slots 16..31 belong to the SQP stages)
     // results of the last QP, aliased onto the matrix area after the ADMM loop
     double* qp_p;                  // step p, kernel order
     double* qp_lam;                // QP multipliers
@@ -129,6 +149,9 @@ struct TS {
     int grow[2 * SH::PO];
     int gn, gfrow, gk, gcol;
     int vk, vcomp, vseg, vloc;
+    // ---- factorisation: the 5 x 5 tile of an augmented segment matrix this thread sweeps in registers (mpcb_qp.h)
+    double tile[25];
+    int tI, tJ, tseg;
 };
 
 // ---- small helpers ------------------------------------------------------------------------------------------------

@@ -39,6 +39,7 @@ inline void fill_limtab(const mpcb_limits* lim, double* t) {
 inline int settings_supported(const mpcb_settings* s, const char** why) {
     if (s->qp_adaptive_rho) { *why = "qp_adaptive_rho=1 is not implemented by the kernels"; return 0; }
     if (s->sqp_max_iter < 1 || s->qp_max_iter < 1 || s->line_search_max_iter < 1) { *why = "iteration limits must be >= 1"; return 0; }
+    if (s->line_search_max_iter > 15) { *why = "line_search_max_iter must be <= 15 (trial-point workspace)"; return 0; }
     if (!(s->poly_order == 3 && s->num_seg == 6)) { *why = "only (poly_order, num_seg) = (3, 6) is instantiated"; return 0; }
     return 1;
 }

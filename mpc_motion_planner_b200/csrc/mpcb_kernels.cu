@@ -1,6 +1,7 @@
 // CUDA kernels (sm_100a) of the batched OCP solver and their launchers.
-//   sqp_stage_kernel: persistent CTAs, one OCP per CTA at a time: linearise + factorise (+ line search and step of the
-//                    previous SQP iteration) out of shared memory -- phases in mpcb_qp.h / mpcb_sqp.h / mpcb_export.h
+//   sqp_stage_kernel: persistent CTAs, one OCP per CTA at a time: load | linearise + factorise + export | line search + step,
+//                    out of shared memory -- phases in mpcb_qp.h / mpcb_sqp.h / mpcb_export.h
+//   node_jac/val_kernel: the per-node rigid-body work (RNEA + derivatives), one thread per node of the whole batch
 //   admm_kernel    : the hot loop, <= 700 box-ADMM iterations per QP with the interior inverses held in registers
 //                    (mpcb_admm.h); QP data handed over through a per-OCP block in global memory
 //   sample_kernel  : read-out + benchmark accounting (get_MPC_trajectory<N>, /root/reference/mpc_solver/motionPlanner.hpp:99-116;
@@ -14,10 +15,12 @@
 
 namespace mpcb {
 
-// Per-OCP workspace in global memory: iterate z (kernel order) | multipliers | flags | QP block (struct AL).
+// Per-OCP workspace in global memory: iterate z (kernel order) | multipliers | flags | node results | QP block (struct AL).
+constexpr int MAX_TRIALS = 16;      // line_search_max_iter + 1 <= 16 (settings_supported)
 template <class SH>
 struct WS {
-    static constexpr int Z = 0, LAM = SH::VP, FLAGS = LAM + SH::NDUAL + 8, QB = FLAGS + 4;
+    static constexpr int Z = 0, LAM = SH::VP, FLAGS = LAM + SH::NDUAL + 8, JG = FLAGS + 4, GJ = JG + SH::NN * 176, GVAL = GJ + SH::NINEQ;
+    static constexpr int QB = GVAL + MAX_TRIALS * SH::NINEQ;
     static constexpr size_t STRIDE = (size_t)QB + AL<SH>::QPBLOCK;
 };
 
@@ -25,6 +28,7 @@ template <class SH>
 __device__ __forceinline__ void bind_problem(Ctx<SH>& c, Problem& pb, const KernelConst& kc, const BatchPtrs& bp, double* ws, int i) {
     c.z = ws + WS<SH>::Z;
     c.lam = ws + WS<SH>::LAM;
+    c.gJg = ws + WS<SH>::JG; c.gGj = ws + WS<SH>::GJ; c.gval = ws + WS<SH>::GVAL;
     pb.limtab = kc.limtab;
     pb.x0 = bp.x0 + (size_t)14 * i; pb.xT = bp.xT + (size_t)14 * i;
     pb.gx = bp.gx + (size_t)14 * SH::NN * i; pb.gu = bp.gu + (size_t)7 * SH::NN * i;
@@ -35,11 +39,11 @@ __device__ __forceinline__ void bind_problem(Ctx<SH>& c, Problem& pb, const Kern
     pb.stats = bp.stats ? bp.stats + i : nullptr;
 }
 
-// stage kernel: it == 0 -> stage_pre, it >= 1 -> stage_post of SQP iteration `it`
+// SQP stage kernel: kind 0 = stage_load, 1 = stage_linfac, 2 = stage_lsstep of SQP iteration `it`
 template <class SH>
 __global__ void __launch_bounds__(NT, 1)
-sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, const int n, const int it, int* __restrict__ counter,
-                 double* __restrict__ workspace) {
+sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, const int n, const int kind, const int it,
+                 int* __restrict__ counter, double* __restrict__ workspace, long long* prof) {
     extern __shared__ double smem[];
     __shared__ int s_next;
     const int tid = threadIdx.x;
@@ -47,6 +51,7 @@ sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, con
     c.bind(smem);
     c.st = &kc.st;
     c.cheb = &kc.cheb;
+    c.prof = prof;
     TS<SH> ts;
     setup_roles(c, ts, tid);
     for (;;) {
@@ -57,12 +62,43 @@ sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, con
         if (i >= n) break;
         double* ws = workspace + WS<SH>::STRIDE * i;
         int* flags = reinterpret_cast<int*>(ws + WS<SH>::FLAGS);
-        if (it > 0 && flags[0]) continue;          // finished in an earlier SQP iteration
+        if (kind != 0 && flags[0]) continue;        // finished in an earlier SQP iteration
         Problem pb;
         bind_problem(c, pb, kc, bp, ws, i);
-        if (it == 0) stage_pre<SH>(c, ts, tid, pb, ws + WS<SH>::QB, flags);
-        else stage_post<SH>(c, ts, tid, pb, ws + WS<SH>::QB, flags, it);
+        if (kind == 0) stage_load<SH>(c, ts, tid, pb, flags);
+        else if (kind == 1) stage_linfac<SH>(c, ts, tid, pb, ws + WS<SH>::QB);
+        else stage_lsstep<SH>(c, ts, tid, pb, ws + WS<SH>::QB, flags, it);
     }
+}
+
+// node kernels: one thread per (OCP, node) resp. (OCP, trial, node) of the whole batch (mpcb_node.h)
+constexpr int NODE_NT = 64;
+template <class SH>
+__global__ void __launch_bounds__(NODE_NT)
+node_jac_kernel(const int n, double* __restrict__ workspace) {
+    const long long e = (long long)blockIdx.x * NODE_NT + threadIdx.x;
+    if (e >= (long long)n * SH::NN) return;
+    const int i = (int)(e / SH::NN), k = (int)(e - (long long)i * SH::NN);
+    double* ws = workspace + WS<SH>::STRIDE * i;
+    if (reinterpret_cast<const int*>(ws + WS<SH>::FLAGS)[0]) return;
+    rbd::DerivScratch S;
+    double Jg[176], g[8];
+    node_jac<SH>(ws + WS<SH>::Z, k, S, Jg, g);
+    for (int j = 0; j < 176; j++) ws[WS<SH>::JG + k * 176 + j] = Jg[j];
+    for (int j = 0; j < 8; j++) ws[WS<SH>::GJ + k * 8 + j] = g[j];
+}
+template <class SH>
+__global__ void __launch_bounds__(NODE_NT)
+node_val_kernel(const int n, const int ntrial, const double tau, double* __restrict__ workspace) {
+    const long long e = (long long)blockIdx.x * NODE_NT + threadIdx.x;
+    const int per = ntrial * SH::NN;
+    if (e >= (long long)n * per) return;
+    const int i = (int)(e / per), r = (int)(e - (long long)i * per), t = r / SH::NN, k = r - t * SH::NN;
+    double* ws = workspace + WS<SH>::STRIDE * i;
+    if (reinterpret_cast<const int*>(ws + WS<SH>::FLAGS)[0]) return;
+    double g[8];
+    node_val<SH>(ws + WS<SH>::Z, ws + WS<SH>::QB + AL<SH>::G_RES, t, tau, k, g);
+    for (int j = 0; j < 8; j++) ws[WS<SH>::GVAL + (t * SH::NN + k) * 8 + j] = g[j];
 }
 
 // the hot kernel: <= qp_max_iter box-ADMM iterations of one QP per CTA at a time
@@ -195,8 +231,20 @@ cudaError_t solve_prepare() {
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(admm_kernel<SH36>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AL<SH36>::BYTES);
 }
-cudaError_t launch_sqp_stage(const KernelConst& kc, const BatchPtrs& bp, int n, int it, int grid, int* counter, double* workspace, cudaStream_t stream) {
-    sqp_stage_kernel<SH36><<<grid, NT, Layout<SH36>::BYTES, stream>>>(kc, bp, n, it, counter, workspace);
+cudaError_t launch_sqp_stage(const KernelConst& kc, const BatchPtrs& bp, int n, int kind, int it, int grid, int* counter, double* workspace,
+                             long long* prof, cudaStream_t stream) {
+    sqp_stage_kernel<SH36><<<grid, NT, Layout<SH36>::BYTES, stream>>>(kc, bp, n, kind, it, counter, workspace, prof);
+    return cudaGetLastError();
+}
+cudaError_t launch_node_jac(int n, double* workspace, cudaStream_t stream) {
+    const long long threads = (long long)n * SH36::NN;
+    node_jac_kernel<SH36><<<(unsigned)((threads + NODE_NT - 1) / NODE_NT), NODE_NT, 0, stream>>>(n, workspace);
+    return cudaGetLastError();
+}
+cudaError_t launch_node_val(const KernelConst& kc, int n, double* workspace, cudaStream_t stream) {
+    const int ntrial = kc.st.line_search_max_iter + 1;
+    const long long threads = (long long)n * ntrial * SH36::NN;
+    node_val_kernel<SH36><<<(unsigned)((threads + NODE_NT - 1) / NODE_NT), NODE_NT, 0, stream>>>(n, ntrial, kc.st.sqp_tau, workspace);
     return cudaGetLastError();
 }
 cudaError_t launch_admm(const KernelConst& kc, int n, int grid, int* counter, double* workspace, long long* prof, cudaStream_t stream) {

@@ -24,8 +24,12 @@ struct BatchPtrs {
 size_t solve_smem_bytes();
 size_t solve_workspace_doubles_per_ocp();
 cudaError_t solve_prepare();
-// it == 0: load + linearise + factorise; it >= 1: line search / step of SQP iteration it (+ next linearisation)
-cudaError_t launch_sqp_stage(const KernelConst& kc, const BatchPtrs& bp, int n, int it, int grid, int* counter, double* workspace, cudaStream_t stream);
+// kind 0: load the guess; kind 1: linearise + factorise + export; kind 2: line search / step of SQP iteration it
+cudaError_t launch_sqp_stage(const KernelConst& kc, const BatchPtrs& bp, int n, int kind, int it, int grid, int* counter, double* workspace,
+                             long long* prof, cudaStream_t stream);
+// per-node rigid-body kernels over the whole batch: Jacobians at the iterate / values at the line-search trial points
+cudaError_t launch_node_jac(int n, double* workspace, cudaStream_t stream);
+cudaError_t launch_node_val(const KernelConst& kc, int n, double* workspace, cudaStream_t stream);
 // prof: 16 cycle counters accumulated by CTA 0 in MPCB_PROFILE builds (may be null)
 cudaError_t launch_admm(const KernelConst& kc, int n, int grid, int* counter, double* workspace, long long* prof, cudaStream_t stream);
 cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double* su, const double* sT, const double* target, int npts,

@@ -19,21 +19,12 @@ namespace mpcb {
 // Linearisation
 // =====================================================================================================================
 template <class SH>
-MPCB_DEV int node_thread(int k) { return (k % 16) * 32 + k / 16; }   // spread the heavy per-node work over warps
-
-template <class SH>
 MPCB_DEV void lin_a(Ctx<SH>& c, TS<SH>& ts, int tid) {
     const double p = c.z[SH::IP], tsc = c.cheb->ts, reg = c.st->hess_reg, rho = c.st->qp_rho;
     if (tid == 0) { c.scal[SC_PBAR] = p; c.scal[SC_MTP] = -tsc * p; }
-    // inequality rows: one node per thread (value + Jacobian), scratch in the (dead) matrix area
-    for (int k = 0; k < SH::NN; k++) {
-        if (node_thread<SH>(k) != tid) continue;
-        double q[7], v[7], u[7], g[8];
-        for (int j = 0; j < 7; j++) { q[j] = c.z[SH::kvar(k, j)]; v[j] = c.z[SH::kvar(k, 7 + j)]; u[j] = c.z[SH::kvar(k, 14 + j)]; }
-        rbd::DerivScratch& S = *reinterpret_cast<rbd::DerivScratch*>(c.sm + Layout<SH>::MAT + k * Layout<SH>::DERIV_STRIDE);
-        rbd::node_constraints_jac(q, v, u, S, g, c.Jg + k * 176);
-        for (int r = 0; r < 8; r++) c.w[SH::NEQ + 8 * k + r] = g[r];
-    }
+    // inequality rows: values + Jacobians were evaluated by node_jac_kernel (mpcb_node.h), one thread per node of the batch
+    for (int e = tid; e < SH::NN * 176; e += NT) c.Jg[e] = c.gJg[e];
+    if (tid < SH::NINEQ) c.w[SH::NEQ + tid] = c.gGj[tid];
     // collocation rows:  sum_l D[j,l] x_{3s+l} - ts p f = 0   (robot_ocp.hpp:64-70 for f)
     if (tid < SH::NEQ) {
         double acc = 0;
@@ -156,35 +147,125 @@ MPCB_DEV void fac_ineq_node(Ctx<SH>& c, int tid, int jn) {
         *aug_ptr(c, s, m, nb, i, jj) += acc;
     }
 }
-// symmetric sweep of pivot kp on every segment's augmented matrix [[S_II, S_IB],[., S_BB]]
+// ---- symmetric sweeps with register-resident tiles ---------------------------------------------------------------------
+// The augmented matrix [[S_II, S_IB],[., S_BB]] of a segment (M = m + nb <= 85) is cut into 5 x 5 tiles of its lower
+// triangle (diagonal tiles are kept full); one thread keeps one tile in registers for all m pivots.  Per pivot the threads
+// that hold the pivot column publish it (and 1/pivot) in shared memory, one barrier, and every thread applies
+//     a_ij -= a_ik a_kj / a_kk  (i, j != k) ;  a_ik = a_ik / a_kk ;  a_kk = -1 / a_kk
+// to its tile: 25 FMAs against 10 shared-memory loads, no index arithmetic in the inner loop.  Three segments are swept at a
+// time (170 threads each); the separator Schur complement C (kind == NS) goes through the same code afterwards.
+// Result: W = -S_II^-1, F = S_II^-1 S_IB, S_BB - S_BI S_II^-1 S_IB  (resp. -C^-1), written back in place.
+constexpr int TILE = 5, SWEEP_SLOT = 170, SWEEP_COLS = 88;
+
 template <class SH>
-MPCB_DEV void fac_sweep_copy(Ctx<SH>& c, int tid, int kp) {
-    constexpr int GS = NT / SH::NS;
-    const int s = tid / GS, lane = tid % GS;
-    if (s >= SH::NS) return;
-    const int m = SH::m(s), nb = SH::nb(s);
-    if (kp >= m) return;
-    double* col = c.colbuf + s * Layout<SH>::COLSTRIDE;
-    for (int e = lane; e < m + nb; e += GS) col[e] = *aug_ptr(c, s, m, nb, e > kp ? e : kp, e > kp ? kp : e);
+MPCB_DEV int sweep_m(int kind) { return kind < SH::NS ? SH::m(kind) : SH::NB; }            // number of pivots
+template <class SH>
+MPCB_DEV int sweep_M(int kind) { return kind < SH::NS ? SH::m(kind) + SH::nb(kind) : SH::NB; }
+template <class SH>
+MPCB_DEV double* sweep_ptr(const Ctx<SH>& c, int kind, int i, int j) {     // entry (i, j), i >= j, of matrix `kind`
+    if (kind < SH::NS) return aug_ptr(c, kind, SH::m(kind), SH::nb(kind), i, j);
+    return c.C + i * (i + 1) / 2 + j;
+}
+// which matrix (or -1) and which tile a thread works on in a round; kinds first..first+count-1 share the CTA
+template <class SH>
+MPCB_DEV void sweep_assign(TS<SH>& ts, int tid, int first, int count) {
+    const int slot = tid / SWEEP_SLOT, t = tid - slot * SWEEP_SLOT;
+    ts.tseg = -1; ts.tI = 0; ts.tJ = 0;
+    if (slot >= count) return;
+    const int kind = first + slot, nt = (sweep_M<SH>(kind) + TILE - 1) / TILE;
+    if (t >= nt * (nt + 1) / 2) return;
+    int I = 0;
+    while ((I + 1) * (I + 2) / 2 <= t) I++;
+    ts.tseg = kind; ts.tI = I; ts.tJ = t - I * (I + 1) / 2;
 }
 template <class SH>
-MPCB_DEV void fac_sweep_update(Ctx<SH>& c, int tid, int kp) {
-    constexpr int GS = NT / SH::NS, TJ = 8, TI = GS / TJ;
-    const int s = tid / GS, lane = tid % GS;
-    if (s >= SH::NS || lane >= TI * TJ) return;
-    const int m = SH::m(s), nb = SH::nb(s), M = m + nb;
-    if (kp >= m) return;
-    const double* col = c.colbuf + s * Layout<SH>::COLSTRIDE;
-    const double dinv = 1.0 / col[kp];
-    for (int i = lane / TJ; i < M; i += TI) {
-        const double ci = col[i] * dinv;
-        for (int j = lane % TJ; j <= i; j += TJ) {
-            double* a = aug_ptr(c, s, m, nb, i, j);
-            if (i == kp) *a = (j == kp) ? -dinv : col[j] * dinv;
-            else if (j == kp) *a = ci;
-            else *a -= ci * col[j];
-        }
+MPCB_DEV double* sweep_col(const Ctx<SH>& c, int kind, int first, int buf) {
+    return c.colbuf + (buf * 3 + (kind - first)) * SWEEP_COLS;
+}
+// publish column kn of the thread's matrix (entries it holds) into buffer buf; rn = kn - 5 * (kn / 5) is static
+template <class SH, int RN>
+MPCB_DEV void sweep_publish(const Ctx<SH>& c, const TS<SH>& ts, int first, int kn, int buf) {
+    const int kind = ts.tseg;
+    if (kind < 0 || kn >= sweep_m<SH>(kind)) return;
+    const int Pn = kn / TILE;
+    double* col = sweep_col(c, kind, first, buf);
+    if (ts.tJ == Pn) {
+        MPCB_UNROLL
+        for (int x = 0; x < TILE; x++) col[TILE * ts.tI + x] = ts.tile[TILE * x + RN];
+        if (ts.tI == Pn) col[SWEEP_COLS - 1] = 1.0 / ts.tile[TILE * RN + RN];
+    } else if (ts.tI == Pn) {
+        MPCB_UNROLL
+        for (int y = 0; y < TILE; y++) col[TILE * ts.tJ + y] = ts.tile[TILE * RN + y];
     }
+}
+template <class SH>
+MPCB_DEV void sweep_load(const Ctx<SH>& c, TS<SH>& ts, int tid, int first, int count) {
+    sweep_assign(ts, tid, first, count);
+    const int kind = ts.tseg;
+    if (kind < 0) return;
+    const int M = sweep_M<SH>(kind);
+    MPCB_UNROLL
+    for (int x = 0; x < TILE; x++)
+        MPCB_UNROLL
+        for (int y = 0; y < TILE; y++) {
+            const int i = TILE * ts.tI + x, j = TILE * ts.tJ + y;
+            const int hi = i > j ? i : j, lo = i > j ? j : i;
+            ts.tile[TILE * x + y] = (hi < M) ? *sweep_ptr(c, kind, hi, lo) : 0.0;
+        }
+    sweep_publish<SH, 0>(c, ts, first, 0, 0);
+}
+// pivot kp = 5 P + R: update the tile from buffer (kp & 1), then publish column kp + 1 into the other buffer
+template <class SH, int R>
+MPCB_DEV void sweep_step(const Ctx<SH>& c, TS<SH>& ts, int first, int P) {
+    const int kind = ts.tseg, kp = TILE * P + R;
+    if (kind < 0 || kp >= sweep_m<SH>(kind)) return;
+    const double* col = sweep_col(c, kind, first, kp & 1);
+    const double dinv = col[SWEEP_COLS - 1];
+    double ci[TILE], cj[TILE];
+    MPCB_UNROLL
+    for (int x = 0; x < TILE; x++) { ci[x] = col[TILE * ts.tI + x] * dinv; cj[x] = col[TILE * ts.tJ + x]; }
+    MPCB_UNROLL
+    for (int x = 0; x < TILE; x++)
+        MPCB_UNROLL
+        for (int y = 0; y < TILE; y++) ts.tile[TILE * x + y] -= ci[x] * cj[y];
+    if (ts.tJ == P) {
+        MPCB_UNROLL
+        for (int x = 0; x < TILE; x++) ts.tile[TILE * x + R] = ci[x];
+    }
+    if (ts.tI == P) {
+        MPCB_UNROLL
+        for (int y = 0; y < TILE; y++) ts.tile[TILE * R + y] = cj[y] * dinv;
+        if (ts.tJ == P) ts.tile[TILE * R + R] = -dinv;
+    }
+    sweep_publish<SH, (R + 1) % TILE>(c, ts, first, kp + 1, (kp + 1) & 1);
+}
+template <class SH>
+MPCB_DEV void sweep_store(const Ctx<SH>& c, const TS<SH>& ts) {
+    const int kind = ts.tseg;
+    if (kind < 0) return;
+    const int M = sweep_M<SH>(kind);
+    MPCB_UNROLL
+    for (int x = 0; x < TILE; x++)
+        MPCB_UNROLL
+        for (int y = 0; y < TILE; y++) {
+            const int i = TILE * ts.tI + x, j = TILE * ts.tJ + y;
+            if (i < M && j <= i) *sweep_ptr(c, kind, i, j) = ts.tile[TILE * x + y];
+        }
+}
+// sweep matrices first .. first+count-1 (count <= 3) over all their pivots
+template <class SH>
+MPCB_DEV void sweep_round(MPCB_DRIVER_PARAMS(SH), int first, int count) {
+    int mmax = 0;
+    for (int k = first; k < first + count; k++) mmax = sweep_m<SH>(k) > mmax ? sweep_m<SH>(k) : mmax;
+    MPCB_PHASE(sweep_load(c, ts, tid, first, count));
+    for (int P = 0; TILE * P < mmax; P++) {
+        MPCB_PHASE(sweep_step<SH, 0>(c, ts, first, P));
+        MPCB_PHASE(sweep_step<SH, 1>(c, ts, first, P));
+        MPCB_PHASE(sweep_step<SH, 2>(c, ts, first, P));
+        MPCB_PHASE(sweep_step<SH, 3>(c, ts, first, P));
+        MPCB_PHASE(sweep_step<SH, 4>(c, ts, first, P));
+    }
+    MPCB_PHASE(sweep_store(c, ts));
 }
 // local boundary column of separator variable b in segment s (or -1)
 template <class SH>
@@ -212,43 +293,21 @@ MPCB_DEV void fac_c_assemble(Ctx<SH>& c, int tid) {
     }
 }
 template <class SH>
-MPCB_DEV void fac_c_copy(Ctx<SH>& c, int tid, int kp) {
-    for (int e = tid; e < SH::NB; e += NT) {
-        const int i = e > kp ? e : kp, j = e > kp ? kp : e;
-        c.colbuf[e] = c.C[i * (i + 1) / 2 + j];
-    }
-}
-template <class SH>
-MPCB_DEV void fac_c_update(Ctx<SH>& c, int tid, int kp) {
-    const double* col = c.colbuf;
-    const double dinv = 1.0 / col[kp];
-    for (int i = tid / 16; i < SH::NB; i += NT / 16) {
-        const double ci = col[i] * dinv;
-        for (int j = tid % 16; j <= i; j += 16) {
-            double* a = c.C + i * (i + 1) / 2 + j;
-            if (i == kp) *a = (j == kp) ? -dinv : col[j] * dinv;
-            else if (j == kp) *a = ci;
-            else *a -= ci * col[j];
-        }
-    }
-}
-
-template <class SH>
 MPCB_DEV void factorise(MPCB_DRIVER_PARAMS(SH)) {
+    static_assert(SH::AUGMAX <= 5 * 17 + 14 && SH::NB <= 85 && 3 * SWEEP_SLOT <= NT && 6 * SWEEP_COLS <= (SH::NS > 1 ? SH::NS : 1) * Layout<SH>::COLSTRIDE,
+                  "sweep tiling: at most 17 x 17 tiles per matrix (170 threads), 3 matrices per round, 6 published columns in colbuf");
+    MPCB_PROF_DECL
     MPCB_PHASE(fac_zero(c, tid));
     MPCB_PHASE(fac_diag(c, ts, tid));
     for (int j = 0; j < SH::PO; j++)
         for (int cc = 0; cc < 14; cc++) MPCB_PHASE(fac_eq_row(c, tid, j, cc));
     for (int jn = 0; jn <= SH::PO; jn++) MPCB_PHASE(fac_ineq_node(c, tid, jn));
-    for (int kp = 0; kp < SH::MMAX; kp++) {
-        MPCB_PHASE(fac_sweep_copy(c, tid, kp));
-        MPCB_PHASE(fac_sweep_update(c, tid, kp));
-    }
+    MPCB_PROF(18)
+    for (int first = 0; first < SH::NS; first += 3) sweep_round<SH>(MPCB_DRIVER_ARGS, first, SH::NS - first < 3 ? SH::NS - first : 3);
+    MPCB_PROF(19)
     MPCB_PHASE(fac_c_assemble(c, tid));
-    for (int kp = 0; kp < SH::NB; kp++) {
-        MPCB_PHASE(fac_c_copy(c, tid, kp));
-        MPCB_PHASE(fac_c_update(c, tid, kp));
-    }
+    sweep_round<SH>(MPCB_DRIVER_ARGS, SH::NS, 1);
+    MPCB_PROF(20)
     // W now holds -S_II^-1 (packed lower, per segment), F = S_II^-1 S_IB, C = -(Schur complement)^-1
 }
 

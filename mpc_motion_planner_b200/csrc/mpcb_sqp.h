@@ -5,6 +5,7 @@
 // and the guess/solution plumbing of MotionPlanner::warm_start_RK / solve_trajectory (motionPlanner.cpp:156-207).
 #pragma once
 #include "mpcb_export.h"
+#include "mpcb_node.h"
 
 namespace mpcb {
 
@@ -42,19 +43,10 @@ MPCB_DEV void sqp_load_b(Ctx<SH>& c, TS<SH>& ts, int tid, const Problem& pb) {
 
 // ---- constraint violation at z + alpha p  (polympc constraints_violation, l1 and max) ------------------
 template <class SH>
-MPCB_DEV void vio_a(Ctx<SH>& c, TS<SH>& ts, int tid, double alpha, bool use_p) {
+MPCB_DEV void vio_a(Ctx<SH>& c, TS<SH>& ts, int tid, double alpha, bool use_p, int trial) {
     const double* P = c.qp_p;
-    for (int k = 0; k < SH::NN; k++) {
-        if (node_thread<SH>(k) != tid) continue;
-        double q[7], v[7], u[7], g[8];
-        for (int j = 0; j < 7; j++) {
-            const int iq = SH::kvar(k, j), iv = SH::kvar(k, 7 + j), iu = SH::kvar(k, 14 + j);
-            q[j] = c.z[iq]; v[j] = c.z[iv]; u[j] = c.z[iu];
-            if (use_p) { q[j] += alpha * P[iq]; v[j] += alpha * P[iv]; u[j] += alpha * P[iu]; }
-        }
-        rbd::node_constraints_value(q, v, u, g);
-        for (int r = 0; r < 8; r++) c.w[SH::NEQ + 8 * k + r] = g[r];
-    }
+    // inequality values at this trial point: evaluated by node_val_kernel (mpcb_node.h)
+    if (tid < SH::NINEQ) c.w[SH::NEQ + tid] = c.gval[trial * SH::NINEQ + tid];
     if (tid < SH::NEQ) {
         double acc = 0;
         MPCB_UNROLL
@@ -106,8 +98,8 @@ MPCB_DEV void vio_d(Ctx<SH>& c, int tid) {
     c.umax[UM_V] = 0;
 }
 template <class SH>
-MPCB_DEV void violation(MPCB_DRIVER_PARAMS(SH), double alpha, bool use_p) {
-    MPCB_PHASE(vio_a(c, ts, tid, alpha, use_p));
+MPCB_DEV void violation(MPCB_DRIVER_PARAMS(SH), double alpha, bool use_p, int trial) {
+    MPCB_PHASE(vio_a(c, ts, tid, alpha, use_p, trial));
     MPCB_PHASE(vio_b(c, tid));
     MPCB_PHASE(vio_c(c, tid));
     MPCB_PHASE(vio_d(c, tid));
@@ -151,31 +143,45 @@ MPCB_DEV void sqp_store(Ctx<SH>& c, TS<SH>& ts, int tid, const Problem& pb) {
     if (tid < SH::NA && pb.slam) pb.slam[tid] = c.lam[tid];
 }
 
-// The solve of one OCP is cut into stages that run as separate kernels (each with its own register budget):
-//   stage_pre   : load the guess, linearise, factorise, export the QP block            (once)
-//   admm_run    : the box-ADMM iterations of the QP (mpcb_admm.h)                      (once per SQP iteration)
-//   stage_post  : line search + step + termination test of SQP iteration `it`; then either the next
-//                 linearisation/factorisation/export, or the final store               (once per SQP iteration)
+// The solve of one OCP is cut into stages that run as separate kernels (each with its own register budget and grid):
+//   stage_load    : guess -> iterate z, multipliers, flags, stats                                      (once)
+//   node_jac      : inequality values + Jacobians at z, one thread per node of the batch (mpcb_node.h)  (per linearisation)
+//   stage_linfac  : rest of the linearisation, KKT factorisation, export of the QP block               (per linearisation)
+//   admm_run      : the box-ADMM iterations of the QP (mpcb_admm.h)                                    (per SQP iteration)
+//   node_val      : inequality values at every line-search trial point z + alpha_t p                  (per SQP iteration)
+//   stage_lsstep  : merit line search, step, termination test of SQP iteration `it`; final store      (per SQP iteration)
 // `flags[0]` (global, per OCP) is set to 1 when the OCP is finished; later stages skip it.  `stats` is written by thread 0.
 template <class SH>
-MPCB_DEV void stage_pre(MPCB_DRIVER_PARAMS(SH), const Problem& pb, double* qb, int* flags) {
+MPCB_DEV void stage_load(MPCB_DRIVER_PARAMS(SH), const Problem& pb, int* flags) {
     mpcb_stats* S = pb.stats;
+    MPCB_PROF_DECL
     MPCB_PHASE(sqp_load_a(c, tid, pb));
     MPCB_PHASE(sqp_load_b(c, ts, tid, pb));
     MPCB_PHASE(if (tid == 0) { flags[0] = 0; if (S) { memset(S, 0, sizeof(mpcb_stats)); S->status = 2; } });
-    linearise<SH>(MPCB_DRIVER_ARGS);
-    factorise<SH>(MPCB_DRIVER_ARGS);
-    export_qp<SH>(MPCB_DRIVER_ARGS, qb);
+    MPCB_PROF(16)
 }
 
 template <class SH>
-MPCB_DEV void stage_post(MPCB_DRIVER_PARAMS(SH), const Problem& pb, double* qb, int* flags, const int it) {
+MPCB_DEV void stage_linfac(MPCB_DRIVER_PARAMS(SH), const Problem& pb, double* qb) {
+    MPCB_PROF_DECL
+    MPCB_PHASE(sqp_load_a(c, tid, pb));
+    linearise<SH>(MPCB_DRIVER_ARGS);
+    MPCB_PROF(17)
+    factorise<SH>(MPCB_DRIVER_ARGS);
+    MPCB_PROF(25)
+    export_qp<SH>(MPCB_DRIVER_ARGS, qb);
+    MPCB_PROF(21)
+}
+
+template <class SH>
+MPCB_DEV void stage_lsstep(MPCB_DRIVER_PARAMS(SH), const Problem& pb, const double* qb, int* flags, const int it) {
     const mpcb_settings& st = *c.st;
     mpcb_stats* S = pb.stats;
+    MPCB_PROF_DECL
     MPCB_PHASE(sqp_load_a(c, tid, pb));
     MPCB_PHASE(import_qp(c, tid, qb));
     MPCB_PHASE(sqp_mu(c, tid));
-    violation<SH>(MPCB_DRIVER_ARGS, 0.0, false);
+    violation<SH>(MPCB_DRIVER_ARGS, 0.0, false, 0);
     MPCB_PHASE(if (tid == 0) {
         const double mu = umax_get(c.umax + UM_B), l1 = c.scal[SC_V_L1];
         c.umax[UM_B] = 0;
@@ -190,22 +196,23 @@ MPCB_DEV void stage_post(MPCB_DRIVER_PARAMS(SH), const Problem& pb, double* qb, 
         }
     });
     // step_size_selection_impl: at most line_search_max_iter-1 trials; the last alpha is returned even if rejected
-    int trials = 0;
+    int trials = 0, trial_used = st.line_search_max_iter;          // index of the step size finally taken (see trial_alpha)
     for (int i = 1; i < st.line_search_max_iter; i++) {
         trials++;
         const double alpha = c.scal[SC_ALPHA];
-        violation<SH>(MPCB_DRIVER_ARGS, alpha, true);
+        violation<SH>(MPCB_DRIVER_ARGS, alpha, true, i);
         MPCB_PHASE(if (tid == 0) {
             const double a = c.scal[SC_ALPHA];
             const double phis = (c.z[SH::IP] + a * c.qp_p[SH::IP]) + c.scal[SC_MU] * c.scal[SC_V_L1];
             if (phis <= c.scal[SC_PHI0] + a * st.sqp_eta * c.scal[SC_DPHI]) c.isc[IS_LS_ACCEPT] = 1;
             else c.scal[SC_ALPHA] = st.sqp_tau * a;
         });
-        if (c.isc[IS_LS_ACCEPT]) break;
+        if (c.isc[IS_LS_ACCEPT]) { trial_used = i; break; }
     }
     const double alpha = c.scal[SC_ALPHA];
+    MPCB_PROF(22)
     MPCB_PHASE(sqp_step(c, tid, alpha));
-    violation<SH>(MPCB_DRIVER_ARGS, 0.0, false);
+    violation<SH>(MPCB_DRIVER_ARGS, 0.0, false, trial_used);      // at the new iterate = the trial point of the step taken
     MPCB_PHASE(if (tid == 0) {
         const double pn = umax_get(c.umax + UM_A), dn = umax_get(c.umax + UM_B);
         c.umax[UM_A] = 0; c.umax[UM_B] = 0;
@@ -218,13 +225,11 @@ MPCB_DEV void stage_post(MPCB_DRIVER_PARAMS(SH), const Problem& pb, double* qb, 
             if (done) S->status = 1;
         }
     });
+    MPCB_PROF(23)
     if (c.isc[IS_SQP_DONE] || it >= st.sqp_max_iter) {      // no re-linearisation after the last step
         MPCB_PHASE({ sqp_store(c, ts, tid, pb); if (tid == 0) flags[0] = 1; });
-        return;
+        MPCB_PROF(24)
     }
-    linearise<SH>(MPCB_DRIVER_ARGS);
-    factorise<SH>(MPCB_DRIVER_ARGS);
-    export_qp<SH>(MPCB_DRIVER_ARGS, qb);
 }
 
 }  // namespace mpcb

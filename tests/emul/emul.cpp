@@ -13,7 +13,7 @@ typedef Shape<3, 6> SH36;
 
 template <class SH>
 struct Emu {
-    std::vector<double> smem, z, lam, qb, asmem;
+    std::vector<double> smem, z, lam, qb, asmem, jg, gj, gval;
     std::vector<TS<SH>> tsv;
     std::vector<ATS<SH>> atsv;
     Ctx<SH> c;
@@ -22,17 +22,30 @@ struct Emu {
     double limtab[40];
     int flags[2];
     Emu(const mpcb_settings* st, const mpcb_limits* lim)
-        : smem(Layout<SH>::TOTAL, 0.0), z(SH::VP, 0.0), lam(SH::NDUAL + 8, 0.0), qb(AL<SH>::QPBLOCK, 0.0), asmem(AL<SH>::TOTAL, 0.0), tsv(NT), atsv(NT) {
+        : smem(Layout<SH>::TOTAL, 0.0), z(SH::VP, 0.0), lam(SH::NDUAL + 8, 0.0), qb(AL<SH>::QPBLOCK, 0.0), asmem(AL<SH>::TOTAL, 0.0), jg(SH::NN * 176, 0.0), gj(SH::NINEQ, 0.0),
+          gval(16 * SH::NINEQ, 0.0), tsv(NT), atsv(NT) {
         mpcb_fill_cheb(SH::PO, SH::NS, &cheb);
         fill_limtab(lim, limtab);
         c.bind(smem.data());
         c.z = z.data(); c.lam = lam.data(); c.st = st; c.cheb = &cheb;
+        c.gJg = jg.data(); c.gGj = gj.data(); c.gval = gval.data(); c.prof = nullptr;
         ac.bind(asmem.data());
         ac.st = st; ac.g = qb.data();
         std::memset(tsv.data(), 0, sizeof(TS<SH>) * NT);
         std::memset(atsv.data(), 0, sizeof(ATS<SH>) * NT);
         for (int tid = 0; tid < NT; tid++) setup_roles(c, tsv[tid], tid);
         flags[0] = flags[1] = 0;
+    }
+    // host stand-ins of node_jac_kernel / node_val_kernel (one "thread" per node / per (trial, node))
+    void node_jac_all() {
+        rbd::DerivScratch S;
+        for (int k = 0; k < SH::NN; k++) node_jac<SH>(z.data(), k, S, jg.data() + k * 176, gj.data() + k * 8);
+    }
+    void node_val_all() {
+        const int ntrial = c.st->line_search_max_iter + 1;
+        for (int t = 0; t < ntrial; t++)
+            for (int k = 0; k < SH::NN; k++)
+                node_val<SH>(z.data(), qb.data() + AL<SH>::G_RES, t, c.st->sqp_tau, k, gval.data() + (t * SH::NN + k) * 8);
     }
 };
 
@@ -57,11 +70,14 @@ int emul_solve(const mpcb_settings* st, const mpcb_limits* lim, int n, const dou
         pb.slam = slam ? slam + (size_t)SH::NDUAL * i : nullptr;
         pb.stats = stats ? stats + i : nullptr;
         // the same kernel sequence mpcb_solve_batch launches
-        stage_pre<SH>(e.c, e.tsv.data(), pb, e.qb.data(), e.flags);
+        stage_load<SH>(e.c, e.tsv.data(), pb, e.flags);
         for (int it = 1; it <= st->sqp_max_iter; it++) {
             if (e.flags[0]) break;
+            e.node_jac_all();
+            stage_linfac<SH>(e.c, e.tsv.data(), pb, e.qb.data());
             admm_run<SH>(e.ac, e.atsv.data());
-            stage_post<SH>(e.c, e.tsv.data(), pb, e.qb.data(), e.flags, it);
+            e.node_val_all();
+            stage_lsstep<SH>(e.c, e.tsv.data(), pb, e.qb.data(), e.flags, it);
         }
     }
     return 0;
@@ -78,7 +94,9 @@ int emul_kkt_apply(const mpcb_settings* st, const mpcb_limits* lim, const double
     Problem pb;
     pb.limtab = e.limtab; pb.x0 = x0; pb.xT = xT; pb.gx = gx.data(); pb.gu = gu.data(); pb.gT = zext[SH::NVAR - 1]; pb.glam = lamext;
     pb.sx = pb.su = pb.sT = dummy.data(); pb.slam = nullptr; pb.stats = nullptr;
-    stage_pre<SH>(e.c, e.tsv.data(), pb, e.qb.data(), e.flags);
+    stage_load<SH>(e.c, e.tsv.data(), pb, e.flags);
+    e.node_jac_all();
+    stage_linfac<SH>(e.c, e.tsv.data(), pb, e.qb.data());
     for (int tid = 0; tid < SH::NVAR; tid++) rhoB[ext_index<SH>(e.tsv[tid].vk, e.tsv[tid].vcomp)] = e.tsv[tid].rhoB;
     for (int r = 0; r < SH::NA; r++) rhoA[r] = e.tsv[r].rho;
     ACtx<SH>& c = e.ac;

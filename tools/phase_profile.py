@@ -19,7 +19,7 @@ s = M.default_settings(); lim = M.default_limits(margins)
 x0, xT = M.generate_problems(lim, 0, 1, n)
 gx, gu, gT = M.guess_batch(s, lim, x0, xT)
 sv = M.Solver(s, lim, device=0)
-out = (C.c_longlong * 16)()
+out = (C.c_longlong * 32)()
 sv.solve(x0, xT, gx, gu, gT)
 sv.L.mpcb_debug_phase_cycles(sv.h, out, 1)
 sx, su, sT, _, st = sv.solve(x0, xT, gx, gu, gT)
@@ -29,8 +29,14 @@ names = ["load", "A rhs", "B interior W/F^T", "B' separator rhs", "C separator s
 cta0_ocps = max(1, round(n / 148))          # CTA 0 handles about n/148 OCPs per ADMM launch
 iters = 2 * 700.0 * cta0_ocps
 tot = sum(out[i] for i in range(1, 8))
-print(f"n={n}  admm kernel ms={sv.last_kernel_ms(1):.3f}  stage ms={sv.last_kernel_ms(0):.3f}  (cycles below: CTA 0, ~{cta0_ocps} OCP(s) x 2 QPs)")
+print(f"n={n}  admm kernel ms={sv.last_kernel_ms(1):.3f}  stage ms={sv.last_kernel_ms(0):.3f}  node ms={sv.last_kernel_ms(2):.3f}  (cycles below: CTA 0, ~{cta0_ocps} OCP(s) x 2 QPs)")
 for i, nm in enumerate(names):
     per = out[i] / iters if 1 <= i <= 7 else out[i] / (2.0 * cta0_ocps)
     print(f"  {nm:26s} {out[i]:14d} cycles   {per:10.1f} per {'iteration' if 1 <= i <= 7 else 'QP'}")
 print(f"  iteration total            {tot / iters:10.1f} cycles")
+stage = {16: "load guess", 17: "linearise (x2)", 18: "KKT assembly (x2)", 19: "interior sweeps (x2)", 20: "separator (x2)", 25: "factorise tail",
+         21: "export (x2)", 22: "merit + line search (x2)", 23: "step + termination (x2)", 24: "store"}
+print("SQP stage kernels, cycles of CTA 0 per OCP (whole solve):")
+for k, nm in stage.items():
+    print(f"  {nm:28s} {out[k] / cta0_ocps:12.0f}")
+print(f"  total                        {sum(out[k] for k in stage) / cta0_ocps:12.0f}")

@@ -144,7 +144,7 @@ int mpcb_last_kernel_launches(const mpcb_handle* h, int kind);
  * ADMM kernel slots: 0 load, 1 rhs, 2 interior W/F^T, 3 separator rhs, 4 separator solve, 5 interior back-substitution,
  * 6 row/box update, 7 residual test, 8 store.  SQP stage slots: 16 load, 17 linearise, 18 KKT assembly, 19 interior sweeps,
  * 20 separator, 21 export, 22 merit + line search, 23 step + termination, 24 store, 25 factorise tail. */
-int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out32, int reset);
+int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out512, int reset);   /* 512 slots; 64.. = per-warp stamps */
 
 /* FP64 FMA peak micro-benchmark on the handle's device (roofline denominator); returns TFLOP/s. */
 double mpcb_measure_fp64_tflops(mpcb_handle* h);

@@ -39,10 +39,12 @@ struct AL {
     static constexpr int I_HD = I_JG + 19 * JGS + 1;   // regularised Hessian diagonal (padded node order)
     static constexpr int I_HA = I_HD + NV;             // Hessian arrow H[p, .]
     static constexpr int I_PCOL = I_HA + NV;           // A[:, p] of the equality rows (256)
-    static constexpr int I_DT = I_PCOL + 256;          // D (16) | -ts*pbar | pad
+    static constexpr int I_PCV = I_PCOL + 256;         // A[r, p] of every row r (416, zero padded)
+    static constexpr int I_FPC = I_PCV + 416;          // F_s[row, p] at the padded-node-order index of the interior variable (416)
+    static constexpr int I_DT = I_FPC + 416;           // D (16) | -ts*pbar | pad
     static constexpr int IMG = I_DT + 24;
     // ---- working vectors behind the image --------------------------------------------------------------------------
-    static constexpr int V_RHS = IMG, V_XT = V_RHS + NV, V_W = V_XT + NV, V_PPV = V_W + NV, V_PARTF = V_PPV + 416, V_RB = V_PARTF + 472;
+    static constexpr int V_RHS = IMG, V_XT = V_RHS + NV, V_W = V_XT + NV, V_PARTF = V_W + NV, V_RB = V_PARTF + 472;
     static constexpr int V_PSUM = V_RB + 72, V_SC = V_PSUM + 64, V_UMAX = V_SC + 8, V_ISC = V_UMAX + UM_COUNT;
     static constexpr int PTID = 416;                   // thread that owns the variable p (lane 0 of warp 13)
     static constexpr int TOTAL = V_ISC + 8;
@@ -147,8 +149,8 @@ MPCB_HD FRole frole(int tid) {
 template <class SH>
 struct ACtx {
     double* sm;
-    double *wovm, *wov5, *F, *C, *Jg, *hd, *ha, *pcol, *dt;
-    double *rhs, *xt, *w, *ppv, *partF, *rB, *psum, *sc;
+    double *wovm, *wov5, *F, *C, *Jg, *hd, *ha, *pcol, *pcv, *fpc, *dt;
+    double *rhs, *xt, *w, *partF, *rB, *psum, *sc;
     unsigned long long* umax;
     long long* isc;
     double* g;                     // this OCP's QP block in global memory
@@ -158,8 +160,8 @@ struct ACtx {
         typedef AL<SH> L;
         sm = smem;
         wovm = sm + L::I_WOVM; wov5 = sm + L::I_WOV5; F = sm + L::I_F; C = sm + L::I_C; Jg = sm + L::I_JG; hd = sm + L::I_HD;
-        ha = sm + L::I_HA; pcol = sm + L::I_PCOL; dt = sm + L::I_DT;
-        rhs = sm + L::V_RHS; xt = sm + L::V_XT; w = sm + L::V_W; ppv = sm + L::V_PPV; partF = sm + L::V_PARTF; rB = sm + L::V_RB;
+        ha = sm + L::I_HA; pcol = sm + L::I_PCOL; pcv = sm + L::I_PCV; fpc = sm + L::I_FPC; dt = sm + L::I_DT;
+        rhs = sm + L::V_RHS; xt = sm + L::V_XT; w = sm + L::V_W; partF = sm + L::V_PARTF; rB = sm + L::V_RB;
         psum = sm + L::V_PSUM; sc = sm + L::V_SC;
         umax = reinterpret_cast<unsigned long long*>(sm + L::V_UMAX);
         isc = reinterpret_cast<long long*>(sm + L::V_ISC);
@@ -258,16 +260,33 @@ MPCB_DEV double pcoef(const ACtx<SH>& c, int r) {
     const int q = r - SH::NEQ;
     return c.Jg[(q >> 3) * AL<SH>::JGS + (q & 7) * 22 + 21];
 }
-// 32 partial sums of a row-indexed vector v (length 416, zero padded) by warp 13: psum[lane] = sum_j v[lane + 32 j]
+// Dot product of two vectors (length 416, zero padded) by the 32 lanes of warp `w`; returned on lane 0 (other lanes: junk).
+// Device: 13 strided products per lane + a 5-step shuffle butterfly.  The host emulation (lanes run one after the other)
+// parks the lane sums in scratch32 and lets the last lane add them; it returns the total on lane 31 instead (`last`).
+MPCB_DEV double tree32(const double* p);
 template <class SH>
-MPCB_DEV void psum32(const ACtx<SH>& c, int tid, const double* v, double* out) {
-    if (tid < AL<SH>::PTID || tid >= AL<SH>::PTID + 32) return;
-    const double* p = v + (tid - AL<SH>::PTID);
-    double a0 = p[0], a1 = p[32], a2 = p[64], a3 = p[96];
-    a0 += p[128]; a1 += p[160]; a2 += p[192]; a3 += p[224];
-    a0 += p[256]; a1 += p[288]; a2 += p[320]; a3 += p[352];
-    a0 += p[384];
-    out[tid - AL<SH>::PTID] = (a0 + a1) + (a2 + a3);
+MPCB_DEV bool warp_vdot(int tid, int w, const double* a, const double* b, double* scratch32, double& out) {
+    if ((tid >> 5) != w) return false;
+    const int lane = tid & 31;
+    const double* p = a + lane;
+    const double* q = b + lane;
+    double a0 = p[0] * q[0], a1 = p[32] * q[32], a2 = p[64] * q[64], a3 = p[96] * q[96];
+    a0 += p[128] * q[128]; a1 += p[160] * q[160]; a2 += p[192] * q[192]; a3 += p[224] * q[224];
+    a0 += p[256] * q[256]; a1 += p[288] * q[288]; a2 += p[320] * q[320]; a3 += p[352] * q[352];
+    a0 += p[384] * q[384];
+    double s = (a0 + a1) + (a2 + a3);
+#ifdef MPCB_EMUL
+    scratch32[lane] = s;
+    if (lane != 31) return false;
+    out = tree32(scratch32);
+    return true;
+#else
+    (void)scratch32;
+    MPCB_UNROLL
+    for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    out = s;
+    return lane == 0;
+#endif
 }
 // sum of 32 values, pairwise tree
 MPCB_DEV double tree32(const double* p) {
@@ -301,7 +320,6 @@ MPCB_DEV void a_load(ACtx<SH>& c, ATS<SH>& ts, int tid) {
         ts.rinvB = 1.0 / ts.rhoB;
     }
     if (tid < L::NV) { c.rhs[tid] = 0; c.xt[tid] = 0; c.w[tid] = 0; }
-    if (tid < 416) c.ppv[tid] = 0;
     ts.zA = ts.yA = ts.x = ts.zB = ts.yB = ts.t = ts.acc = ts.acc2 = 0;     // boxADMM starts cold (warm_start = false)
     if (tid < 72) c.rB[tid] = 0;
     if (tid < 472) c.partF[tid] = 0;
@@ -315,19 +333,38 @@ template <class SH>
 MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     int i, k, comp;
     if (vrole<SH>(tid, i, k, comp)) {
-        const double g = (k >= 0) ? col_times(c, k, comp, c.w) : 0.0;     // p: the gather arrives through psum in phase B'
+        const double g = (k >= 0) ? col_times(c, k, comp, c.w) : 0.0;     // p: the gather arrives through sc[0] in phase B2
         const double h = (k < 0) ? 1.0 : 0.0;              // gradient of the Mayer cost p (robot_ocp.hpp:206)
         c.rhs[i] = c.st->qp_sigma * ts.x - h + ts.rhoB * ts.zB - ts.yB + g;
     }
-    psum32(c, tid, c.ppv, c.psum);
+    double s;
+    if (warp_vdot<SH>(tid, 13, c.pcv, c.w, c.psum, s)) c.sc[0] = s;       // (A^T w)_p = sum_r A[r,p] w_r
 }
 
-// ---- phase B: t = W rhs_I (register-resident rows) and part = F^T rhs_I ----------------------------------------------
+// ---- phase B1: part = F^T rhs_I --------------------------------------------------------------------------------------
 template <class SH>
-MPCB_DEV void b_interior(ACtx<SH>& c, ATS<SH>& ts, int tid) {
+MPCB_DEV void b_ft(ACtx<SH>& c, int tid) {
+    typedef AL<SH> L;
+    const FRole f = frole<SH>(tid);
+    if (f.unit >= 0 && f.col < SH::nb(f.seg) - 1) {       // the p column is summed through fpv (phase A) instead
+        const double* Fc = c.F + L::foff(f.seg) + f.col * L::fld(f.seg) + f.r0;
+        const double* b = c.rhs + L::ibase(f.seg) + f.r0;
+        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        MPCB_UNROLL
+        for (int i = 0; i < 16; i += 4) {       // every chunk has at least 15 rows
+            const d2 v = ld2(b + i), v2 = ld2(b + i + 2);
+            a0 += Fc[i] * v.a; a1 += Fc[i + 1] * v.b; a2 += Fc[i + 2] * v2.a;
+            if (i + 3 < f.len) a3 += Fc[i + 3] * v2.b;
+        }
+        if (f.len > 16) { const d2 v = ld2(b + 16); a0 += Fc[16] * v.a; a1 += Fc[17] * v.b; }
+        c.partF[f.unit] = (a0 + a1) + (a2 + a3);
+    }
+}
+// ---- phase B2: t = W rhs_I from the register-resident rows (runs in the same barrier interval as the separator rhs) ---
+template <class SH>
+MPCB_DEV void b_w(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
     const WRole r = wrole<SH>(tid);
-    const FRole f = frole<SH>(tid);
     if (r.paired) {
         const double* b = c.rhs + L::ibase(r.seg) + 2 * r.half;
         double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
@@ -360,41 +397,16 @@ MPCB_DEV void b_interior(ACtx<SH>& c, ATS<SH>& ts, int tid) {
         a0 += wo[16 * 224] * v.a; a1 += wo[17 * 224] * v.b;
         ts.acc = (a0 + a1) + (a2 + a3);
     }
-    if (f.unit >= 0) {
-        const double* Fc = c.F + L::foff(f.seg) + f.col * L::fld(f.seg) + f.r0;
-        const double* b = c.rhs + L::ibase(f.seg) + f.r0;
-        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-        MPCB_UNROLL
-        for (int i = 0; i < 16; i += 4) {       // every chunk has at least 15 rows
-            const d2 v = ld2(b + i), v2 = ld2(b + i + 2);
-            a0 += Fc[i] * v.a; a1 += Fc[i + 1] * v.b; a2 += Fc[i + 2] * v2.a;
-            if (i + 3 < f.len) a3 += Fc[i + 3] * v2.b;
-        }
-        if (f.len > 16) { const d2 v = ld2(b + 16); a0 += Fc[16] * v.a; a1 += Fc[17] * v.b; }
-        c.partF[f.unit] = (a0 + a1) + (a2 + a3);
-    }
 }
 // ---- phase B': separator right-hand side r_B = rhs_B - sum_s (F_s^T rhs_I) -------------------------------------------
 template <class SH>
 MPCB_DEV void b_seprhs(ACtx<SH>& c, int tid) {
     typedef AL<SH> L;
-    if (tid >= SH::NB) return;
-    if (tid == SH::NB - 1) {
-        // p: gather of A[:,p]^T w (32 partial sums of phase A) and the last boundary column of every segment
-        double r = c.rhs[L::IP] + tree32(c.psum);
-        double q[6];
-        MPCB_UNROLL
-        for (int s = 0; s < SH::NS; s++) {
-            const double* pf = c.partF + pfoff<SH>(s) + (SH::nb(s) - 1);
-            const int nb = SH::nb(s);
-            double v = pf[0] + pf[nb];
-            v += (s == 0 || s == 5) ? (pf[2 * nb] + pf[3 * nb]) : pf[2 * nb];
-            q[s] = v;
-        }
-        r -= ((q[0] + q[1]) + (q[2] + q[3])) + (q[4] + q[5]);
-        c.rB[tid] = r;
-        return;
+    {   // p: r_B[p] = rhs_p + (A^T w)_p - (F^T rhs_I)_p ; the second dot product over all interior variables by warp 15
+        double s;
+        if (warp_vdot<SH>(tid, 15, c.fpc, c.rhs, c.psum + 32, s)) c.rB[SH::NB - 1] = (c.rhs[L::IP] + c.sc[0]) - s;
     }
+    if (tid >= SH::NB - 1) return;
     const int sj = tid / 14 + 1, cc = tid - 14 * (sj - 1);     // junction x_{3 sj}: right boundary of segment sj-1, left of sj
     const int sp = sj - 1, nbp = SH::nb(sp), nbo = SH::nb(sj);
     const double* pp = c.partF + pfoff<SH>(sp) + (sp > 0 ? 14 : 0) + cc;
@@ -467,9 +479,7 @@ MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
         const double zn = dmin(dmax(zh + ts.yA * ts.rinv, ts.l), ts.u);
         ts.yA += ts.rho * (zh - zn);
         ts.zA = zn;
-        const double w = ts.rho * ts.zA - ts.yA;
-        c.w[tid] = w;
-        c.ppv[tid] = pcoef(c, tid) * w;
+        c.w[tid] = ts.rho * ts.zA - ts.yA;
     }
     int i, k, comp;
     if (vrole<SH>(tid, i, k, comp)) {
@@ -485,8 +495,8 @@ MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 template <class SH>
 MPCB_DEV void chk_a(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
-    if (tid < SH::NA) { c.rhs[tid] = ts.yA; c.partF[tid] = pcoef(c, tid) * ts.yA; }      // rhs / partF are free until the next phase A / B
-    else if (tid < 416) c.partF[tid] = 0;
+    if (tid < SH::NA) c.rhs[tid] = ts.yA;       // the rhs slot is free until the next phase A
+    else if (tid < 416) c.rhs[tid] = 0;
     int i, k, comp;
     if (vrole<SH>(tid, i, k, comp)) c.xt[i] = ts.x;
 }
@@ -507,7 +517,7 @@ MPCB_DEV void chk_b(ACtx<SH>& c, ATS<SH>& ts, int tid) {
             naty = fabs(aty); nhx = fabs(hx); rd = fabs(hx + aty);
         }
     }
-    psum32(c, tid, c.partF, c.psum);                    // (A^T y)_p
+    { double s; if (warp_vdot<SH>(tid, 13, c.pcv, c.rhs, c.psum, s)) c.sc[2] = s; }   // (A^T y)_p
     if (tid >= NT - 32) {
         double s = 0;
         for (int j = tid - (NT - 32); j < L::IP; j += 32) s += c.ha[j] * c.xt[j];     // H[p,.] x ; pads hold zeros
@@ -520,7 +530,7 @@ template <class SH>
 MPCB_DEV void chk_c(ACtx<SH>& c, ATS<SH>& ts, int tid, int iter) {
     typedef AL<SH> L;
     if (tid != L::PTID) return;
-    const double s1 = tree32(c.psum), s2 = tree32(c.psum + 32);
+    const double s1 = c.sc[2], s2 = tree32(c.psum + 32);
     const double aty = s1 + ts.yB, hx = c.hd[L::IP] * ts.x + s2;
     const double rd = dmax(umax_get(c.umax + UM_RD), fabs(hx + 1.0 + aty));
     const double nhx = dmax(umax_get(c.umax + UM_NHX), fabs(hx)), naty = dmax(umax_get(c.umax + UM_NATY), fabs(aty));
@@ -549,6 +559,15 @@ MPCB_DEV void a_finish(ACtx<SH>& c, ATS<SH>& ts, int tid, int max_iter) {
     }
 }
 
+// Per-warp time stamps of one iteration (MPCB_PROFILE builds): slot s, warp w -> prof[64 + 16 s + w] = clock at the END of
+// the warp's work in phase s (before the barrier); slot 15 holds the common origin (after the barrier that starts phase A).
+#if defined(MPCB_PROFILE) && !defined(MPCB_EMUL)
+#define MPCB_WSTAMP(slot)                                                                                        \
+    if (iter == 100 && blockIdx.x == 0 && c.prof && (tid & 31) == 0) c.prof[64 + 16 * (slot) + (tid >> 5)] = clock64();
+#else
+#define MPCB_WSTAMP(slot)
+#endif
+
 // One QP: load the block, iterate, store the result.
 template <class SH>
 MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
@@ -558,21 +577,26 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
     MPCB_PROF(0)
     const int max_iter = c.st->qp_max_iter, chk = c.st->qp_check_termination;
     for (int iter = 1; iter <= max_iter; iter++) {
-        MPCB_PHASE(a_rhs(c, ts, tid));
+        MPCB_WSTAMP(15)
+        MPCB_PHASE({ a_rhs(c, ts, tid); MPCB_WSTAMP(0) });
         MPCB_PROF(1)
-        MPCB_PHASE_NS(b_interior(c, ts, tid));
+        MPCB_PHASE({ b_ft(c, tid); MPCB_WSTAMP(1) });
+        MPCB_PROF(2)
+        // the separator right-hand side (71 threads, latency bound) shares its barrier interval with t = W rhs_I
+        MPCB_PHASE_NS(b_seprhs(c, tid));
+        MPCB_PHASE_NS(b_w(c, ts, tid));
         MPCB_PHASE({
             const double o = MPCB_PEER(acc, 1);
             ts.t = wrole<SH>(tid).paired ? ts.acc + o : ts.acc;
+            MPCB_WSTAMP(2)
         });
-        MPCB_PROF(2)
-        MPCB_PHASE(b_seprhs(c, tid));
         MPCB_PROF(3)
         MPCB_PHASE_NS(c_separator(c, ts, tid));
         MPCB_PHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
         MPCB_PHASE({
             const double s4 = ts.acc2 + MPCB_PEER(acc2, 2);
             if (tid < 4 * SH::NB && (tid & 3) == 0) c.xt[L::sepidx(tid >> 2)] = s4;
+            MPCB_WSTAMP(3)
         });
         MPCB_PROF(4)
         MPCB_PHASE_NS(d_interior(c, ts, tid));
@@ -581,9 +605,11 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
             const WRole r = wrole<SH>(tid);
             const double fx = r.paired ? ts.acc + o : ts.acc;
             if (r.valid && r.half == 0) c.xt[r.out] = ts.t - fx;
+            MPCB_WSTAMP(4)
         });
         MPCB_PROF(5)
-        MPCB_PHASE(e_update(c, ts, tid));
+        MPCB_PHASE({ e_update(c, ts, tid); MPCB_WSTAMP(5) });
+        MPCB_WSTAMP(6)
         MPCB_PROF(6)
         if (chk > 0 && iter % chk == 0) {
             MPCB_PHASE(chk_a(c, ts, tid));

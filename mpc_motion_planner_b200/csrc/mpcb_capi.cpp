@@ -93,7 +93,7 @@ int mpcb_create(const mpcb_settings* s, int device, mpcb_handle** out) {
     }
     if ((e = solve_prepare()) != cudaSuccess) return fail("cudaFuncSetAttribute(solve kernels)", e);
     h->grid_max = h->sm_count;      // one CTA per SM (shared memory bound)
-    if ((e = cudaMalloc(&h->d_prof, 32 * sizeof(long long))) != cudaSuccess || (e = cudaMemset(h->d_prof, 0, 32 * sizeof(long long))) != cudaSuccess) return fail("cudaMalloc(prof)", e);
+    if ((e = cudaMalloc(&h->d_prof, 512 * sizeof(long long))) != cudaSuccess || (e = cudaMemset(h->d_prof, 0, 512 * sizeof(long long))) != cudaSuccess) return fail("cudaMalloc(prof)", e);
     if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
     *out = h;
     return MPCB_OK;
@@ -317,12 +317,12 @@ double mpcb_last_kernel_ms(mpcb_handle* h, int kind) {
     }
     return total;
 }
-int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out32, int reset) {
+int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out32, int reset) {   // 512 slots: 0..31 phases, 64.. per-warp stamps
     if (!h || !out32) return MPCB_ERR_BAD_ARG;
     CK(cudaSetDevice(h->device));
     CK(cudaDeviceSynchronize());
-    CK(cudaMemcpy(out32, h->d_prof, 32 * sizeof(long long), cudaMemcpyDeviceToHost));
-    if (reset) CK(cudaMemset(h->d_prof, 0, 32 * sizeof(long long)));
+    CK(cudaMemcpy(out32, h->d_prof, 512 * sizeof(long long), cudaMemcpyDeviceToHost));
+    if (reset) CK(cudaMemset(h->d_prof, 0, 512 * sizeof(long long)));
     return MPCB_OK;
 }
 int mpcb_last_kernel_launches(const mpcb_handle* h, int kind) {

@@ -86,6 +86,17 @@ MPCB_DEV void exp_vec(const Ctx<SH>& c, const TS<SH>& ts, int tid, double* qb) {
         if (tid < SH::NEQ) qb[L::G_ROW + 3 * L::NV + tid] = ts.pc;
     }
     if (tid < 256) img[L::I_PCOL + tid] = (tid < SH::NEQ) ? c.pcol[tid] : 0.0;
+    if (tid < 416) {
+        // A[r, p] of every row; F_s[row, p] at the padded-node-order index of every interior variable
+        img[L::I_PCV + tid] = tid < SH::NEQ ? c.pcol[tid] : (tid < SH::NA ? c.Jg[(tid - SH::NEQ) * 22 + 21] : 0.0);
+        int k, comp;
+        double fp = 0.0;
+        if (tid < L::IP && L::decode(tid, k, comp)) {
+            const int s = k / 3 > 5 ? 5 : k / 3, row = tid - L::ibase(s);
+            if (s == 0 || row >= 0) fp = c.F[SH::foff(s) + row * SH::nb(s) + (SH::nb(s) - 1)];
+        }
+        img[L::I_FPC + tid] = fp;
+    }
     if (tid < 24) img[L::I_DT + tid] = (tid < 16) ? c.cheb->D[tid >> 2][tid & 3] : (tid == 16 ? c.scal[SC_MTP] : 0.0);
 }
 template <class SH>

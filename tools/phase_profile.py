@@ -19,7 +19,7 @@ s = M.default_settings(); lim = M.default_limits(margins)
 x0, xT = M.generate_problems(lim, 0, 1, n)
 gx, gu, gT = M.guess_batch(s, lim, x0, xT)
 sv = M.Solver(s, lim, device=0)
-out = (C.c_longlong * 32)()
+out = (C.c_longlong * 512)()
 sv.solve(x0, xT, gx, gu, gT)
 sv.L.mpcb_debug_phase_cycles(sv.h, out, 1)
 sx, su, sT, _, st = sv.solve(x0, xT, gx, gu, gT)
@@ -40,3 +40,11 @@ print("SQP stage kernels, cycles of CTA 0 per OCP (whole solve):")
 for k, nm in stage.items():
     print(f"  {nm:28s} {out[k] / cta0_ocps:12.0f}")
 print(f"  total                        {sum(out[k] for k in stage) / cta0_ocps:12.0f}")
+
+names2 = ["A rhs", "B1 F^T", "B2 W + sep rhs", "C separator", "D back-subst", "E update"]
+t0 = min(out[64 + 16 * 15 + w] for w in range(16))
+print("per-warp end-of-work times in iteration 100 of CTA 0 (cycles after the start of phase A; then the barrier):")
+for s_, nm in enumerate(names2):
+    ends = [out[64 + 16 * s_ + w] - t0 for w in range(16)]
+    print(f"  {nm:16s} " + " ".join(f"{e:5d}" for e in ends))
+print(f"  {'after E barrier':16s} " + " ".join(f"{out[64 + 16 * 6 + w] - t0:5d}" for w in range(16)))

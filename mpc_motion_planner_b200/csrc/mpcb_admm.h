@@ -19,6 +19,7 @@
 // The QP data arrives from the factorisation kernel through a per-OCP block in global memory (layout: struct AL).
 #pragma once
 #include "mpcb_ctx.h"
+#include "mpcb_tmem.h"
 
 namespace mpcb {
 
@@ -28,13 +29,7 @@ struct AL {
     static constexpr int SEG = 66, NV = 416, IP = 414;  // padded node order: segment stride, length, index of p
     static constexpr int WREG = 32;                    // W coefficients per thread held in registers
     // ---- shared-memory image (copied verbatim from the global QP block) --------------------------------------------
-    static constexpr int I_WOVM = 0;                   // [18][224]  columns 32..49 of the middle-segment rows
-    static constexpr int I_WOV5 = I_WOVM + 18 * 224;   // [4][160]   tail columns of the last segment's half rows
-    static constexpr int I_F = I_WOV5 + 4 * 160;       // F_s column-major with odd leading dimension
-    static constexpr int FMID = 29 * 49 + 4;            // middle F_s padded so that consecutive segments continue the bank sequence
-    static constexpr int FSZ = 15 * 63 + 4 * FMID + 15 * 71;
-    static constexpr int I_C = I_F + FSZ;              // [18][284]  C^-1, 4 lanes per row
-    static constexpr int I_JG = I_C + 18 * 284;        // 19 nodes x (8 x 22), node stride 177
+    static constexpr int I_JG = 0;                     // 19 nodes x (8 x 22), node stride 177
     static constexpr int JGS = 177;
     static constexpr int I_HD = I_JG + 19 * JGS + 1;   // regularised Hessian diagonal (padded node order)
     static constexpr int I_HA = I_HD + NV;             // Hessian arrow H[p, .]
@@ -43,6 +38,19 @@ struct AL {
     static constexpr int I_FPC = I_PCV + 416;          // F_s[row, p] at the padded-node-order index of the interior variable (416)
     static constexpr int I_DT = I_FPC + 416;           // D (16) | -ts*pbar | pad
     static constexpr int IMG = I_DT + 24;
+    // ---- thread-private strips in tensor memory (mpcb_tmem.h), slot = one double -----------------------------------
+    //   warps 0..3   (segment-0 row pairs) : consts 0..7 | F half row 8..15 | F^T chunk 16..33 | C^-1 quarter row 34..51
+    //   warps 4..10  (middle-segment rows) : consts 0..7 | W columns 32..48 8..24 | F row 25..53 | F^T chunk 54..71
+    //   warps 11..15 (segment-5 row pairs) : consts 0..7 | W tail 8..11 | F half row 12..19 | F^T chunk 20..37 | C^-1 quarter row 38..55
+    // consts = l, u, rho, 1/rho of the thread's row | lb, ub, rho_b, 1/rho_b of the thread's variable
+    static constexpr int TM_CST = 0;
+    MPCB_HD static int tm_size(int w) { return (w >= 4 && w <= 10) ? 72 : 56; }
+    MPCB_HD static int tm_wov(int tid) { return 8; }
+    MPCB_HD static int tm_frow(int tid) { return tid < 128 ? 8 : (tid < 352 ? 25 : 12); }
+    MPCB_HD static int tm_ft(int tid) { return tid < 128 ? 16 : (tid < 352 ? 54 : 20); }
+    MPCB_HD static int tm_c(int tid) { return tid < 128 ? 34 : 38; }
+    // C^-1 unit of a thread (4 units per separator row): threads 0..127 and 352..511, -1 elsewhere / beyond 4 NB
+    MPCB_HD static int cunit(int tid) { const int u = tid < 128 ? tid : (tid >= 352 ? tid - 224 : -1); return u < 4 * SH::NB ? u : -1; }
     // ---- working vectors behind the image --------------------------------------------------------------------------
     static constexpr int V_RHS = IMG, V_XT = V_RHS + NV, V_W = V_XT + NV, V_PARTF = V_W + NV, V_RB = V_PARTF + 472;
     static constexpr int V_PSUM = V_RB + 72, V_SC = V_PSUM + 64, V_UMAX = V_SC + 8, V_ISC = V_UMAX + UM_COUNT;
@@ -51,15 +59,12 @@ struct AL {
     static constexpr size_t BYTES = (size_t)TOTAL * 8;
     // ---- global QP block ---------------------------------------------------------------------------------------------
     static constexpr int G_WREG = 0;                   // [32][NT]
-    static constexpr int G_IMG = G_WREG + WREG * NT;
-    static constexpr int G_ROW = G_IMG + IMG;          // l | u | rho | pc   (NV each, row order)
-    static constexpr int G_VAR = G_ROW + 4 * NV;       // lb | ub | rho_b    (NV each, padded node order)
-    static constexpr int G_RES = G_VAR + 3 * NV;       // step p (kernel order, VP) | multipliers (NDUAL+4) | info (4)
+    static constexpr int G_TM = G_WREG + WREG * NT;    // [TM_SLOTS][NT]  the strips, slot-major
+    static constexpr int G_IMG = G_TM + TM_SLOTS * NT;
+    static constexpr int G_RES = G_IMG + IMG;       // step p (kernel order, VP) | multipliers (NDUAL+4) | info (4)
     static constexpr int R_LAM = SH::VP, R_INFO = SH::VP + SH::NDUAL + 4;
     static constexpr int QPBLOCK = G_RES + R_INFO + 4;
 
-    MPCB_HD static int fld(int s) { return s == 0 ? 63 : (s == 5 ? 71 : 49); }                  // leading dimension of F_s
-    MPCB_HD static int foff(int s) { return s == 0 ? 0 : 15 * 63 + (s - 1) * FMID; }
     MPCB_HD static int vidx(int k, int comp) { const int s = k / 3 > 5 ? 5 : k / 3; return SEG * s + 21 * (k - 3 * s) + comp; }
     MPCB_HD static int sepidx(int b) { return b < 70 ? SEG * (b / 14 + 1) + b % 14 : IP; }
     MPCB_HD static int ibase(int s) { return s == 0 ? 0 : SEG * s + 14; }                        // first interior index of segment s
@@ -149,7 +154,7 @@ MPCB_HD FRole frole(int tid) {
 template <class SH>
 struct ACtx {
     double* sm;
-    double *wovm, *wov5, *F, *C, *Jg, *hd, *ha, *pcol, *pcv, *fpc, *dt;
+    double *Jg, *hd, *ha, *pcol, *pcv, *fpc, *dt;
     double *rhs, *xt, *w, *partF, *rB, *psum, *sc;
     unsigned long long* umax;
     long long* isc;
@@ -159,7 +164,7 @@ struct ACtx {
     MPCB_HD void bind(double* smem) {
         typedef AL<SH> L;
         sm = smem;
-        wovm = sm + L::I_WOVM; wov5 = sm + L::I_WOV5; F = sm + L::I_F; C = sm + L::I_C; Jg = sm + L::I_JG; hd = sm + L::I_HD;
+        Jg = sm + L::I_JG; hd = sm + L::I_HD;
         ha = sm + L::I_HA; pcol = sm + L::I_PCOL; pcv = sm + L::I_PCV; fpc = sm + L::I_FPC; dt = sm + L::I_DT;
         rhs = sm + L::V_RHS; xt = sm + L::V_XT; w = sm + L::V_W; partF = sm + L::V_PARTF; rB = sm + L::V_RB;
         psum = sm + L::V_PSUM; sc = sm + L::V_SC;
@@ -174,9 +179,16 @@ struct ACtx {
 template <class SH>
 struct ATS {
     double wreg[AL<SH>::WREG];
-    double l, u, rho, rinv, zA, yA;        // row role (thread r < NA); rinv = 1 / rho
-    double x, zB, yB, lb, ub, rhoB, rinvB; // variable role (thread i < 404 in padded node order; p on thread PTID)
+    double zA, yA;                         // row role (thread r < NA); l, u, rho, 1/rho live in the thread's TMEM strip
+    double x, zB, yB, rhoB;                // variable role (thread i < 404 in padded node order; p on thread PTID); lb, ub, 1/rho_b in TMEM
     double t, acc, acc2;                   // interior row: W rhs_I ; cross-lane exchange slots
+#ifdef MPCB_EMUL
+    double tm[TM_SLOTS];                   // host emulation of the thread's TMEM strip
+    const double* tma() const { return tm; }
+#else
+    uint32_t tmaddr;                       // TMEM address of the thread's strip (lane quadrant | first column)
+    __device__ __forceinline__ uint32_t tma() const { return tmaddr; }
+#endif
 };
 
 #ifdef MPCB_EMUL
@@ -308,17 +320,20 @@ MPCB_DEV void a_load(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     const double* g = c.g;
     MPCB_UNROLL
     for (int e = 0; e < L::WREG; e++) ts.wreg[e] = g[L::G_WREG + e * NT + tid];
+    // the thread's strip: global (slot-major, coalesced over tid) -> tensor memory, 8 slots per store
+    const int nslot = L::tm_size(tid >> 5);
+    for (int q = 0; q < nslot; q += 8) {
+        double v[8];
+        MPCB_UNROLL
+        for (int j = 0; j < 8; j++) v[j] = g[L::G_TM + (q + j) * NT + tid];
+#ifdef MPCB_EMUL
+        for (int j = 0; j < 8; j++) ts.tm[q + j] = v[j];
+#else
+        tm_st8(ts.tmaddr, q, v);
+#endif
+    }
+    ts.rhoB = g[L::G_TM + (L::TM_CST + 6) * NT + tid];
     for (int e = 2 * tid; e < L::IMG; e += 2 * NT) { c.sm[e] = g[L::G_IMG + e]; c.sm[e + 1] = g[L::G_IMG + e + 1]; }
-    ts.l = ts.u = 0; ts.rho = ts.rinv = 1; ts.lb = ts.ub = 0; ts.rhoB = ts.rinvB = 1;
-    if (tid < SH::NA) {
-        ts.l = g[L::G_ROW + tid]; ts.u = g[L::G_ROW + L::NV + tid]; ts.rho = g[L::G_ROW + 2 * L::NV + tid];
-        ts.rinv = 1.0 / ts.rho;
-    }
-    int i, k, comp;
-    if (vrole<SH>(tid, i, k, comp)) {
-        ts.lb = g[L::G_VAR + i]; ts.ub = g[L::G_VAR + L::NV + i]; ts.rhoB = g[L::G_VAR + 2 * L::NV + i];
-        ts.rinvB = 1.0 / ts.rhoB;
-    }
     if (tid < L::NV) { c.rhs[tid] = 0; c.xt[tid] = 0; c.w[tid] = 0; }
     ts.zA = ts.yA = ts.x = ts.zB = ts.yB = ts.t = ts.acc = ts.acc2 = 0;     // boxADMM starts cold (warm_start = false)
     if (tid < 72) c.rB[tid] = 0;
@@ -326,6 +341,9 @@ MPCB_DEV void a_load(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     if (tid < 64) c.psum[tid] = 0;
     if (tid < UM_COUNT) c.umax[tid] = 0;
     if (tid == 0) { c.isc[IS_QP_DONE] = 0; c.isc[IS_QP_STATUS] = 2; c.isc[IS_QP_ITERS] = 0; }
+#ifndef MPCB_EMUL
+    tm_wait_st();
+#endif
 }
 
 // ---- phase A: rhs = sigma x - h + rho_b z_b - y_b + A^T w ;  warp 13 folds the products A[r,p] w_r into 32 partial sums ----
@@ -343,20 +361,30 @@ MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 
 // ---- phase B1: part = F^T rhs_I --------------------------------------------------------------------------------------
 template <class SH>
-MPCB_DEV void b_ft(ACtx<SH>& c, int tid) {
+MPCB_DEV void b_ft(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
     const FRole f = frole<SH>(tid);
+    // the unit's 18 coefficients F_s[r0 + i, col] (zero beyond the chunk) come from the thread's TMEM strip; tcgen05.ld is
+    // warp-collective, so every lane loads (idle lanes hold zeros) and only the use is predicated
+    TmBuf<8> f0, f1;
+    TmBuf<2> f2;
+    const int so = L::tm_ft(tid);
+    tm_ld(ts.tma(), so, f0); tm_ld(ts.tma(), so + 8, f1); tm_ld(ts.tma(), so + 16, f2);
+    tm_wait(f0, f1, f2);
     if (f.unit >= 0 && f.col < SH::nb(f.seg) - 1) {       // the p column is summed through fpv (phase A) instead
-        const double* Fc = c.F + L::foff(f.seg) + f.col * L::fld(f.seg) + f.r0;
         const double* b = c.rhs + L::ibase(f.seg) + f.r0;
         double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
         MPCB_UNROLL
-        for (int i = 0; i < 16; i += 4) {       // every chunk has at least 15 rows
+        for (int i = 0; i < 8; i += 4) {
             const d2 v = ld2(b + i), v2 = ld2(b + i + 2);
-            a0 += Fc[i] * v.a; a1 += Fc[i + 1] * v.b; a2 += Fc[i + 2] * v2.a;
-            if (i + 3 < f.len) a3 += Fc[i + 3] * v2.b;
+            a0 += f0.get(i) * v.a; a1 += f0.get(i + 1) * v.b; a2 += f0.get(i + 2) * v2.a; a3 += f0.get(i + 3) * v2.b;
         }
-        if (f.len > 16) { const d2 v = ld2(b + 16); a0 += Fc[16] * v.a; a1 += Fc[17] * v.b; }
+        MPCB_UNROLL
+        for (int i = 0; i < 8; i += 4) {
+            const d2 v = ld2(b + 8 + i), v2 = ld2(b + 8 + i + 2);
+            a0 += f1.get(i) * v.a; a1 += f1.get(i + 1) * v.b; a2 += f1.get(i + 2) * v2.a; a3 += f1.get(i + 3) * v2.b;
+        }
+        { const d2 v = ld2(b + 16); a0 += f2.get(0) * v.a; a1 += f2.get(1) * v.b; }
         c.partF[f.unit] = (a0 + a1) + (a2 + a3);
     }
 }
@@ -367,6 +395,8 @@ MPCB_DEV void b_w(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     const WRole r = wrole<SH>(tid);
     if (r.paired) {
         const double* b = c.rhs + L::ibase(r.seg) + 2 * r.half;
+        TmBuf<4> wo;                                   // segment 5: columns 64 + 2 half, +1, 68 + 2 half, +1 of the row
+        if (r.seg == 5) tm_ld(ts.tma(), L::tm_wov(tid), wo);
         double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
         MPCB_UNROLL
         for (int q = 0; q < 16; q += 2) {
@@ -374,27 +404,36 @@ MPCB_DEV void b_w(ACtx<SH>& c, ATS<SH>& ts, int tid) {
             a0 += ts.wreg[2 * q] * v.a; a1 += ts.wreg[2 * q + 1] * v.b; a2 += ts.wreg[2 * q + 2] * v2.a; a3 += ts.wreg[2 * q + 3] * v2.b;
         }
         if (r.seg == 5) {
-            const double* wo = c.wov5 + (tid - 352);
             const d2 v = ld2(b + 64), v2 = ld2(b + 68);
-            a0 += wo[0] * v.a; a1 += wo[160] * v.b; a2 += wo[320] * v2.a; a3 += wo[480] * v2.b;
+            tm_wait(wo);
+            a0 += wo.get(0) * v.a; a1 += wo.get(1) * v.b; a2 += wo.get(2) * v2.a; a3 += wo.get(3) * v2.b;
         }
         ts.acc = (a0 + a1) + (a2 + a3);
     } else {
         const double* b = c.rhs + L::ibase(r.seg);
+        TmBuf<8> w0, w1;                               // columns 32..47 of the row
+        TmBuf<1> w2;                                   // column 48
+        const int so = L::tm_wov(tid);
+        tm_ld(ts.tma(), so, w0);
         double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
         MPCB_UNROLL
         for (int e = 0; e < L::WREG; e += 4) {
             const d2 v = ld2(b + e), v2 = ld2(b + e + 2);
             a0 += ts.wreg[e] * v.a; a1 += ts.wreg[e + 1] * v.b; a2 += ts.wreg[e + 2] * v2.a; a3 += ts.wreg[e + 3] * v2.b;
         }
-        const double* wo = c.wovm + (tid - 128);
+        tm_ld(ts.tma(), so + 8, w1); tm_ld(ts.tma(), so + 16, w2);
+        tm_wait(w0, w1, w2);
         MPCB_UNROLL
-        for (int e = 0; e < 16; e += 4) {
+        for (int e = 0; e < 8; e += 4) {
             const d2 v = ld2(b + 32 + e), v2 = ld2(b + 34 + e);
-            a0 += wo[e * 224] * v.a; a1 += wo[(e + 1) * 224] * v.b; a2 += wo[(e + 2) * 224] * v2.a; a3 += wo[(e + 3) * 224] * v2.b;
+            a0 += w0.get(e) * v.a; a1 += w0.get(e + 1) * v.b; a2 += w0.get(e + 2) * v2.a; a3 += w0.get(e + 3) * v2.b;
         }
-        const d2 v = ld2(b + 48);
-        a0 += wo[16 * 224] * v.a; a1 += wo[17 * 224] * v.b;
+        MPCB_UNROLL
+        for (int e = 0; e < 8; e += 4) {
+            const d2 v = ld2(b + 40 + e), v2 = ld2(b + 42 + e);
+            a0 += w1.get(e) * v.a; a1 += w1.get(e + 1) * v.b; a2 += w1.get(e + 2) * v2.a; a3 += w1.get(e + 3) * v2.b;
+        }
+        a0 += w2.get(0) * b[48];
         ts.acc = (a0 + a1) + (a2 + a3);
     }
 }
@@ -419,16 +458,29 @@ MPCB_DEV void b_seprhs(ACtx<SH>& c, int tid) {
 // ---- phase C: x~_B = C^-1 r_B, 4 lanes per row ------------------------------------------------------------------------
 template <class SH>
 MPCB_DEV void c_separator(ACtx<SH>& c, ATS<SH>& ts, int tid) {
+    typedef AL<SH> L;
     double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-    if (tid < 4 * SH::NB) {
-        const double* Cr = c.C + tid;
+    const int cu = L::cunit(tid);
+    if (tid < 128 || tid >= 352) {                      // warp-uniform: tcgen05.ld is warp-collective
+        // unit cu: row cu / 4 of C^-1, columns 4 jj + cu % 4 (jj = 0..17, zero beyond NB) from the thread's TMEM strip
+        // (the four spare lanes of warp 15 hold zeros)
+        TmBuf<8> c0, c1;
+        TmBuf<2> c2;
+        const int so = L::tm_c(tid);
+        tm_ld(ts.tma(), so, c0); tm_ld(ts.tma(), so + 8, c1); tm_ld(ts.tma(), so + 16, c2);
         const double* rb = c.rB + (tid & 3);
+        tm_wait(c0, c1, c2);
         MPCB_UNROLL
-        for (int jj = 0; jj < 16; jj += 4) {
-            a0 += Cr[jj * 284] * rb[4 * jj]; a1 += Cr[(jj + 1) * 284] * rb[4 * jj + 4];
-            a2 += Cr[(jj + 2) * 284] * rb[4 * jj + 8]; a3 += Cr[(jj + 3) * 284] * rb[4 * jj + 12];
+        for (int jj = 0; jj < 8; jj += 4) {
+            a0 += c0.get(jj) * rb[4 * jj]; a1 += c0.get(jj + 1) * rb[4 * jj + 4];
+            a2 += c0.get(jj + 2) * rb[4 * jj + 8]; a3 += c0.get(jj + 3) * rb[4 * jj + 12];
         }
-        a0 += Cr[16 * 284] * rb[64]; a1 += Cr[17 * 284] * rb[68];
+        MPCB_UNROLL
+        for (int jj = 0; jj < 8; jj += 4) {
+            a0 += c1.get(jj) * rb[32 + 4 * jj]; a1 += c1.get(jj + 1) * rb[32 + 4 * jj + 4];
+            a2 += c1.get(jj + 2) * rb[32 + 4 * jj + 8]; a3 += c1.get(jj + 3) * rb[32 + 4 * jj + 12];
+        }
+        a0 += c2.get(0) * rb[64]; a1 += c2.get(1) * rb[68];
     }
     ts.acc = (a0 + a1) + (a2 + a3);
 }
@@ -437,34 +489,44 @@ template <class SH>
 MPCB_DEV void d_interior(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
     const WRole r = wrole<SH>(tid);
-    const int s = r.seg, ld = L::fld(s);
-    const double* Fr = c.F + L::foff(s) + r.row;
+    const int s = r.seg, so = L::tm_frow(tid);
     double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-    if (s == 0 || s == 5) {
-        // 15 boundary columns: 14 junction states + p, split over the two lanes of the row (8 | 7)
+    if (r.paired) {
+        // 15 boundary columns: 14 junction states + p, split over the two lanes of the row (8 | 7); strip: F[row, 8 half + j]
+        TmBuf<8> fh;
+        tm_ld(ts.tma(), so, fh);
         const double* xj = c.xt + (s == 0 ? L::SEG : 5 * L::SEG) + 8 * r.half;
-        const double* Fh = Fr + 8 * r.half * ld;
         const d2 v0 = ld2(xj), v1 = ld2(xj + 2), v2 = ld2(xj + 4);
-        a0 += Fh[0] * v0.a; a1 += Fh[ld] * v0.b; a2 += Fh[2 * ld] * v1.a; a3 += Fh[3 * ld] * v1.b;
-        a0 += Fh[4 * ld] * v2.a; a1 += Fh[5 * ld] * v2.b;
-        if (r.half == 0) { const d2 v3 = ld2(xj + 6); a2 += Fh[6 * ld] * v3.a; a3 += Fh[7 * ld] * v3.b; }
-        else a2 += Fh[6 * ld] * c.xt[L::IP];
+        const double xp = c.xt[L::IP];
+        tm_wait(fh);
+        a0 += fh.get(0) * v0.a; a1 += fh.get(1) * v0.b; a2 += fh.get(2) * v1.a; a3 += fh.get(3) * v1.b;
+        a0 += fh.get(4) * v2.a; a1 += fh.get(5) * v2.b;
+        if (r.half == 0) { const d2 v3 = ld2(xj + 6); a2 += fh.get(6) * v3.a; a3 += fh.get(7) * v3.b; }
+        else a2 += fh.get(6) * xp;
     } else {
+        // strip: the 29 boundary columns of the row (left junction 0..13, right junction 14..27, p)
+        TmBuf<8> f0, f1, f2;
+        TmBuf<4> f3;
+        TmBuf<1> f4;
+        tm_ld(ts.tma(), so, f0); tm_ld(ts.tma(), so + 8, f1);
         const double* x1 = c.xt + L::SEG * s;
         const double* x2 = c.xt + L::SEG * (s + 1);
+        tm_wait(f0, f1);
+        tm_ld(ts.tma(), so + 16, f2); tm_ld(ts.tma(), so + 24, f3); tm_ld(ts.tma(), so + 28, f4);
         MPCB_UNROLL
-        for (int cc = 0; cc < 12; cc += 4) {
+        for (int cc = 0; cc < 8; cc += 4) {
             const d2 v = ld2(x1 + cc), v2 = ld2(x1 + cc + 2);
-            a0 += Fr[cc * ld] * v.a; a1 += Fr[(cc + 1) * ld] * v.b; a2 += Fr[(cc + 2) * ld] * v2.a; a3 += Fr[(cc + 3) * ld] * v2.b;
+            a0 += f0.get(cc) * v.a; a1 += f0.get(cc + 1) * v.b; a2 += f0.get(cc + 2) * v2.a; a3 += f0.get(cc + 3) * v2.b;
         }
-        { const d2 v = ld2(x1 + 12); a0 += Fr[12 * ld] * v.a; a1 += Fr[13 * ld] * v.b; }
-        MPCB_UNROLL
-        for (int cc = 0; cc < 12; cc += 4) {
-            const d2 v = ld2(x2 + cc), v2 = ld2(x2 + cc + 2);
-            a0 += Fr[(14 + cc) * ld] * v.a; a1 += Fr[(15 + cc) * ld] * v.b; a2 += Fr[(16 + cc) * ld] * v2.a; a3 += Fr[(17 + cc) * ld] * v2.b;
-        }
-        { const d2 v = ld2(x2 + 12); a2 += Fr[26 * ld] * v.a; a3 += Fr[27 * ld] * v.b; }
-        a0 += Fr[28 * ld] * c.xt[L::IP];
+        { const d2 v = ld2(x1 + 8), v2 = ld2(x1 + 10); a0 += f1.get(0) * v.a; a1 += f1.get(1) * v.b; a2 += f1.get(2) * v2.a; a3 += f1.get(3) * v2.b; }
+        { const d2 v = ld2(x1 + 12); a0 += f1.get(4) * v.a; a1 += f1.get(5) * v.b; }
+        { const d2 v = ld2(x2); a0 += f1.get(6) * v.a; a1 += f1.get(7) * v.b; }
+        tm_wait(f2, f3, f4);
+        { const d2 v = ld2(x2 + 2); a2 += f2.get(0) * v.a; a3 += f2.get(1) * v.b; }
+        { const d2 v = ld2(x2 + 4), v2 = ld2(x2 + 6); a0 += f2.get(2) * v.a; a1 += f2.get(3) * v.b; a2 += f2.get(4) * v2.a; a3 += f2.get(5) * v2.b; }
+        { const d2 v = ld2(x2 + 8); a0 += f2.get(6) * v.a; a1 += f2.get(7) * v.b; }
+        { const d2 v = ld2(x2 + 10), v2 = ld2(x2 + 12); a2 += f3.get(0) * v.a; a3 += f3.get(1) * v.b; a2 += f3.get(2) * v2.a; a3 += f3.get(3) * v2.b; }
+        a0 += f4.get(0) * c.xt[L::IP];
     }
     ts.acc = r.valid ? (a0 + a1) + (a2 + a3) : 0.0;
 }
@@ -472,22 +534,28 @@ MPCB_DEV void d_interior(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 // y/rho is evaluated as y * (1/rho) with the reciprocal taken once per QP (an FP64 division costs ~130 cycles of latency).
 template <class SH>
 MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
+    typedef AL<SH> L;
     const double al = c.st->qp_alpha;
+    TmBuf<8> k;                                  // l, u, rho, 1/rho | lb, ub, rho_b, 1/rho_b
+    tm_ld(ts.tma(), L::TM_CST, k);
+    double ax = 0, xt = 0;
+    if (tid < SH::NA) ax = row_times(c, tid, c.xt);
+    int i, kk, comp;
+    const bool var = vrole<SH>(tid, i, kk, comp);
+    if (var) xt = c.xt[i];
+    tm_wait(k);
     if (tid < SH::NA) {
-        const double ax = row_times(c, tid, c.xt);
         const double zh = al * ax + (1 - al) * ts.zA;
-        const double zn = dmin(dmax(zh + ts.yA * ts.rinv, ts.l), ts.u);
-        ts.yA += ts.rho * (zh - zn);
+        const double zn = dmin(dmax(zh + ts.yA * k.get(3), k.get(0)), k.get(1));
+        ts.yA += k.get(2) * (zh - zn);
         ts.zA = zn;
-        c.w[tid] = ts.rho * ts.zA - ts.yA;
+        c.w[tid] = k.get(2) * ts.zA - ts.yA;
     }
-    int i, k, comp;
-    if (vrole<SH>(tid, i, k, comp)) {
-        const double xt = c.xt[i];
+    if (var) {
         ts.x = al * xt + (1 - al) * ts.x;
         const double zh = al * xt + (1 - al) * ts.zB;
-        const double zn = dmin(dmax(zh + ts.yB * ts.rinvB, ts.lb), ts.ub);
-        ts.yB += ts.rhoB * (zh - zn);
+        const double zn = dmin(dmax(zh + ts.yB * k.get(7), k.get(4)), k.get(5));
+        ts.yB += k.get(6) * (zh - zn);
         ts.zB = zn;
     }
 }
@@ -580,7 +648,7 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
         MPCB_WSTAMP(15)
         MPCB_PHASE({ a_rhs(c, ts, tid); MPCB_WSTAMP(0) });
         MPCB_PROF(1)
-        MPCB_PHASE({ b_ft(c, tid); MPCB_WSTAMP(1) });
+        MPCB_PHASE({ b_ft(c, ts, tid); MPCB_WSTAMP(1) });
         MPCB_PROF(2)
         // the separator right-hand side (71 threads, latency bound) shares its barrier interval with t = W rhs_I
         MPCB_PHASE_NS(b_seprhs(c, tid));
@@ -595,7 +663,8 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
         MPCB_PHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
         MPCB_PHASE({
             const double s4 = ts.acc2 + MPCB_PEER(acc2, 2);
-            if (tid < 4 * SH::NB && (tid & 3) == 0) c.xt[L::sepidx(tid >> 2)] = s4;
+            const int cu = L::cunit(tid);
+            if (cu >= 0 && (cu & 3) == 0) c.xt[L::sepidx(cu >> 2)] = s4;
             MPCB_WSTAMP(3)
         });
         MPCB_PROF(4)

@@ -15,8 +15,8 @@ MPCB_DEV double sym_packed(const double* P, int i, int j) {
     return P[hi * (hi + 1) / 2 + lo];
 }
 
-// W rows: 32 coefficients per ADMM thread (register part) + the overflow columns of the middle / last segments.
-// The factorisation holds -S_II^-1 (packed lower, per segment); the ADMM kernel wants +S_II^-1.
+// W rows: 32 coefficients per ADMM thread (register part); the overflow columns of the middle / last segments go to the
+// thread's TMEM strip.  The factorisation holds -S_II^-1 (packed lower, per segment); the ADMM kernel wants +S_II^-1.
 template <class SH>
 MPCB_DEV void exp_w(const Ctx<SH>& c, int tid, double* qb) {
     typedef AL<SH> L;
@@ -26,36 +26,46 @@ MPCB_DEV void exp_w(const Ctx<SH>& c, int tid, double* qb) {
         const int col = wcol<SH>(r, e);
         qb[L::G_WREG + e * NT + tid] = col >= 0 ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
     }
-    double* img = qb + L::G_IMG;
-    if (tid >= 128 && tid < 352) {
-        for (int e = 0; e < 18; e++) {
-            const int col = wcol<SH>(r, 32 + e);
-            img[L::I_WOVM + e * 224 + (tid - 128)] = col >= 0 ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
-        }
-    } else if (tid >= 352) {
-        for (int e = 0; e < 4; e++) {
-            const int col = wcol<SH>(r, 32 + e);
-            img[L::I_WOV5 + e * 160 + (tid - 352)] = col >= 0 ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
-        }
+    double* tm = qb + L::G_TM + tid;
+    const int nov = tid < 128 ? 0 : (tid < 352 ? 17 : 4);
+    for (int e = 0; e < nov; e++) {
+        const int col = wcol<SH>(r, 32 + e);
+        tm[(L::tm_wov(tid) + e) * NT] = col >= 0 ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
     }
 }
-// F_s (row-major i*nb + col in the factorisation) -> column-major with odd leading dimension; C^-1 -> 4 lanes per row
+// F_s (row-major i*nb + col in the factorisation) -> per-thread pieces in the TMEM strips: the row (or half row) the
+// thread multiplies in phase D, the column chunk it multiplies in phase B1; C^-1 -> 4 units per row; the inequality
+// Jacobian stays in the shared-memory image
 template <class SH>
 MPCB_DEV void exp_fc(const Ctx<SH>& c, int tid, double* qb) {
     typedef AL<SH> L;
     double* img = qb + L::G_IMG;
-    for (int e = tid; e < L::FSZ; e += NT) {
-        double v = 0.0;
-        {
-            const int s = e < 945 ? 0 : (e < 945 + 4 * L::FMID ? 1 + (e - 945) / L::FMID : 5);
-            const int off = e - L::foff(s), ld = L::fld(s), col = off / ld, i = off - col * ld;
-            if (i < SH::m(s) && col < SH::nb(s)) v = c.F[SH::foff(s) + i * SH::nb(s) + col];
+    double* tm = qb + L::G_TM + tid;
+    {
+        const WRole r = wrole<SH>(tid);
+        const double* Fs = c.F + SH::foff(r.seg) + r.row * SH::nb(r.seg);
+        const int so = L::tm_frow(tid);
+        if (r.paired) {
+            for (int j = 0; j < 8; j++) {
+                const int col = 8 * r.half + j;
+                tm[(so + j) * NT] = (r.valid && col < SH::nb(r.seg)) ? Fs[col] : 0.0;
+            }
+        } else {
+            for (int j = 0; j < 29; j++) tm[(so + j) * NT] = r.valid ? Fs[j] : 0.0;
         }
-        img[L::I_F + e] = v;
     }
-    for (int e = tid; e < 18 * 284; e += NT) {
-        const int jj = e / 284, t = e - jj * 284, b = t >> 2, col = 4 * jj + (t & 3);
-        img[L::I_C + e] = (col < SH::NB) ? -sym_packed<SH>(c.C, b, col) : 0.0;
+    {
+        const FRole f = frole<SH>(tid);
+        const int so = L::tm_ft(tid);
+        for (int i = 0; i < 18; i++)
+            tm[(so + i) * NT] = (f.unit >= 0 && i < f.len) ? c.F[SH::foff(f.seg) + (f.r0 + i) * SH::nb(f.seg) + f.col] : 0.0;
+    }
+    if (tid < 128 || tid >= 352) {
+        const int cu = L::cunit(tid), so = L::tm_c(tid);
+        for (int jj = 0; jj < 18; jj++) {
+            const int col = 4 * jj + (tid & 3);
+            tm[(so + jj) * NT] = (cu >= 0 && col < SH::NB) ? -sym_packed<SH>(c.C, cu >> 2, col) : 0.0;
+        }
     }
     for (int e = tid; e < 19 * L::JGS + 1; e += NT) {
         const int k = e / L::JGS, o = e - k * L::JGS;
@@ -67,23 +77,26 @@ template <class SH>
 MPCB_DEV void exp_vec(const Ctx<SH>& c, const TS<SH>& ts, int tid, double* qb) {
     typedef AL<SH> L;
     double* img = qb + L::G_IMG;
+    double* tm = qb + L::G_TM;
     if (tid < L::NV) {
         int k, comp;
-        if (!L::decode(tid, k, comp)) {       // pads
-            img[L::I_HD + tid] = 0; img[L::I_HA + tid] = 0;
-            qb[L::G_VAR + tid] = 0; qb[L::G_VAR + L::NV + tid] = 0; qb[L::G_VAR + 2 * L::NV + tid] = 0;
-        }
-        if (tid >= SH::NA) { qb[L::G_ROW + tid] = 0; qb[L::G_ROW + L::NV + tid] = 0; qb[L::G_ROW + 2 * L::NV + tid] = 0; }
-        if (tid >= SH::NEQ) qb[L::G_ROW + 3 * L::NV + tid] = 0;
+        if (!L::decode(tid, k, comp)) { img[L::I_HD + tid] = 0; img[L::I_HA + tid] = 0; }       // pads
     }
-    if (tid < SH::NVAR) {                     // thread tid owns variable tid (kernel order)
+    {   // constants of ADMM threads that own no row / no variable
+        int i, k, comp;
+        if (tid >= SH::NA) { tm[(L::TM_CST + 0) * NT + tid] = 0; tm[(L::TM_CST + 1) * NT + tid] = 0; tm[(L::TM_CST + 2) * NT + tid] = 1; tm[(L::TM_CST + 3) * NT + tid] = 1; }
+        if (!vrole<SH>(tid, i, k, comp)) { tm[(L::TM_CST + 4) * NT + tid] = 0; tm[(L::TM_CST + 5) * NT + tid] = 0; tm[(L::TM_CST + 6) * NT + tid] = 1; tm[(L::TM_CST + 7) * NT + tid] = 1; }
+    }
+    if (tid < SH::NVAR) {                     // thread tid owns variable tid (kernel order); its ADMM thread is the padded-node-order index
         const int i = (ts.vk < 0) ? L::IP : L::vidx(ts.vk, ts.vcomp);
+        const int at = (ts.vk < 0) ? L::PTID : i;
         img[L::I_HD + i] = ts.hd; img[L::I_HA + i] = ts.ha;
-        qb[L::G_VAR + i] = ts.lb; qb[L::G_VAR + L::NV + i] = ts.ub; qb[L::G_VAR + 2 * L::NV + i] = ts.rhoB;
+        tm[(L::TM_CST + 4) * NT + at] = ts.lb; tm[(L::TM_CST + 5) * NT + at] = ts.ub;
+        tm[(L::TM_CST + 6) * NT + at] = ts.rhoB; tm[(L::TM_CST + 7) * NT + at] = 1.0 / ts.rhoB;
     }
     if (tid < SH::NA) {
-        qb[L::G_ROW + tid] = ts.l; qb[L::G_ROW + L::NV + tid] = ts.u; qb[L::G_ROW + 2 * L::NV + tid] = ts.rho;
-        if (tid < SH::NEQ) qb[L::G_ROW + 3 * L::NV + tid] = ts.pc;
+        tm[(L::TM_CST + 0) * NT + tid] = ts.l; tm[(L::TM_CST + 1) * NT + tid] = ts.u;
+        tm[(L::TM_CST + 2) * NT + tid] = ts.rho; tm[(L::TM_CST + 3) * NT + tid] = 1.0 / ts.rho;
     }
     if (tid < 256) img[L::I_PCOL + tid] = (tid < SH::NEQ) ? c.pcol[tid] : 0.0;
     if (tid < 416) {

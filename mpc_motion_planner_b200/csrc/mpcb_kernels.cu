@@ -107,12 +107,20 @@ __global__ void __launch_bounds__(NT, 1)
 admm_kernel(const __grid_constant__ KernelConst kc, const int n, int* __restrict__ counter, double* __restrict__ workspace, long long* prof) {
     extern __shared__ double smem[];
     __shared__ int s_next;
+    __shared__ uint32_t s_tmem;
     const int tid = threadIdx.x;
     ACtx<SH> c;
     c.bind(smem);
     c.st = &kc.st;
     c.prof = prof;
     ATS<SH> ts;
+    // all 512 TMEM columns of the SM for this CTA (one CTA per SM): thread-private operand strips, mpcb_tmem.h
+    if (tid < 32) tm_alloc512(&s_tmem);
+    tm_fence_before();
+    __syncthreads();
+    tm_fence_after();
+    const uint32_t tmem_base = s_tmem;
+    ts.tmaddr = tmem_base + ((uint32_t)(32 * ((tid >> 5) & 3)) << 16) + 2 * tm_warp_base(tid >> 5);
     for (;;) {
         if (tid == 0) s_next = atomicAdd(counter, 1);
         __syncthreads();
@@ -124,6 +132,9 @@ admm_kernel(const __grid_constant__ KernelConst kc, const int n, int* __restrict
         c.g = ws + WS<SH>::QB;
         admm_run<SH>(c, ts, tid);
     }
+    tm_fence_before();
+    __syncthreads();
+    if (tid < 32) tm_free512(tmem_base);
 }
 
 // ---- read-out + accounting ------------------------------------------------------------------------------------------

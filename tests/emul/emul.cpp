@@ -107,13 +107,13 @@ int emul_kkt_apply(const mpcb_settings* st, const mpcb_limits* lim, const double
         if (L::decode(i, k, comp)) c.rhs[i] = rhs[ext_index<SH>(k, comp)];
     }
     c.sc[0] = 0;        // no A^T w gather in this test: rhs is given directly
-    MPCB_PHASE(b_ft(c, tid));
+    MPCB_PHASE(b_ft(c, ts, tid));
     MPCB_PHASE_NS(b_seprhs(c, tid));
     MPCB_PHASE_NS(b_w(c, ts, tid));
     MPCB_PHASE({ const double o = MPCB_PEER(acc, 1); ts.t = wrole<SH>(tid).paired ? ts.acc + o : ts.acc; });
     MPCB_PHASE_NS(c_separator(c, ts, tid));
     MPCB_PHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
-    MPCB_PHASE({ const double s4 = ts.acc2 + MPCB_PEER(acc2, 2); if (tid < 4 * SH::NB && (tid & 3) == 0) c.xt[L::sepidx(tid >> 2)] = s4; });
+    MPCB_PHASE({ const double s4 = ts.acc2 + MPCB_PEER(acc2, 2); const int cu = L::cunit(tid); if (cu >= 0 && (cu & 3) == 0) c.xt[L::sepidx(cu >> 2)] = s4; });
     MPCB_PHASE_NS(d_interior(c, ts, tid));
     MPCB_PHASE({
         const double o = MPCB_PEER(acc, 1);

@@ -1,0 +1,8 @@
+# quick GPU check: parity tests, bench without the CPU leg, per-phase cycle profile (outputs under gpurun_out/)
+TAG=${1:-quick}
+cd $GRAFT_REPO_ROOT
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_gputests.log 2>&1; echo "pytest exit $?"; tail -5 gpurun_out/${TAG}_gputests.log
+timeout 600 python bench.py --no-cpu-baseline > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "bench exit $?"
+python -c "
+import json;d=json.load(open('gpurun_out/${TAG}_bench.json'));print(d['value'],d['ms_per_step'],d['roofline']['frac'],d['roofline']['step'])"
+MPCB_LIB=mpc_motion_planner_b200/libmpcb_prof.so timeout 300 python tools/phase_profile.py 148 > gpurun_out/${TAG}_phase_cycles.txt 2>&1; cat gpurun_out/${TAG}_phase_cycles.txt

@@ -70,6 +70,15 @@ __global__ void k_tmem(double* out, long long* cyc, int* ok) {
         const double e = 1.0 + 1e-6 * (tid * 64 + 16 + 1);
         if (d != e) atomicAdd(ok, 1);
     }
+    // loads at column offsets that are not multiples of the load width (the ADMM kernel packs uneven per-thread pieces)
+    for (int off = 1; off < 40; off += 3) {         // offset in doubles (2 columns each)
+        ldtm16(v, mine + 2 * off);
+        wait_ld();
+        for (int j = 0; j < 8; j++) {
+            const double d = __longlong_as_double(((long long)v[2 * j + 1] << 32) | v[2 * j]);
+            if (d != 1.0 + 1e-6 * (tid * 64 + off + j)) atomicAdd(ok, 1);
+        }
+    }
     __syncthreads();
     double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
     double x[16];

@@ -29,9 +29,13 @@ struct AL {
     static constexpr int SEG = 66, NV = 416, IP = 414;  // padded node order: segment stride, length, index of p
     static constexpr int WREG = 32;                    // W coefficients per thread held in registers
     // ---- shared-memory image (copied verbatim from the global QP block) --------------------------------------------
-    static constexpr int I_JG = 0;                     // 19 nodes x (8 x 22), node stride 177
-    static constexpr int JGS = 177;
-    static constexpr int I_HD = I_JG + 19 * JGS + 1;   // regularised Hessian diagonal (padded node order)
+    // inequality Jacobian, twice: row-major for A x (row stride 26, node stride 208; a row starts one slot late when its
+    // node's first variable sits on an odd index, so that 16-byte loads of the row line up with 16-byte loads of x) and
+    // transposed for A^T y (8 row entries per variable, stride 10, node stride 210).  The strides keep the eight 16-byte
+    // pieces of a quarter warp on distinct bank groups.
+    static constexpr int I_JG = 0, JGR = 26, JGS = 8 * JGR;
+    static constexpr int I_GT = I_JG + 19 * JGS, GTC = 10, GTS = 21 * GTC;
+    static constexpr int I_HD = I_GT + 19 * GTS;       // regularised Hessian diagonal (padded node order)
     static constexpr int I_HA = I_HD + NV;             // Hessian arrow H[p, .]
     static constexpr int I_PCOL = I_HA + NV;           // A[:, p] of the equality rows (256)
     static constexpr int I_PCV = I_PCOL + 256;         // A[r, p] of every row r (416, zero padded)
@@ -154,7 +158,7 @@ MPCB_HD FRole frole(int tid) {
 template <class SH>
 struct ACtx {
     double* sm;
-    double *Jg, *hd, *ha, *pcol, *pcv, *fpc, *dt;
+    double *Jg, *Gt, *hd, *ha, *pcol, *pcv, *fpc, *dt;
     double *rhs, *xt, *w, *partF, *rB, *psum, *sc;
     unsigned long long* umax;
     long long* isc;
@@ -164,7 +168,7 @@ struct ACtx {
     MPCB_HD void bind(double* smem) {
         typedef AL<SH> L;
         sm = smem;
-        Jg = sm + L::I_JG; hd = sm + L::I_HD;
+        Jg = sm + L::I_JG; Gt = sm + L::I_GT; hd = sm + L::I_HD;
         ha = sm + L::I_HA; pcol = sm + L::I_PCOL; pcv = sm + L::I_PCV; fpc = sm + L::I_FPC; dt = sm + L::I_DT;
         rhs = sm + L::V_RHS; xt = sm + L::V_XT; w = sm + L::V_W; partF = sm + L::V_PARTF; rB = sm + L::V_RB;
         psum = sm + L::V_PSUM; sc = sm + L::V_SC;
@@ -234,43 +238,47 @@ MPCB_DEV double row_times(const ACtx<SH>& c, int r, const double* x) {
         return (a0 + a1) + a2;
     }
     const int q = r - SH::NEQ, k = q >> 3, rr = q & 7;
-    const double* G = c.Jg + k * L::JGS + rr * 22;
-    const double* xs = x + L::vidx(k, 0);
-    double a0 = 0, a1 = 0, a2 = 0, a3 = G[21] * x[L::IP];
+    const double* G = c.Jg + k * L::JGS + rr * L::JGR;
+    const double* xs = x + (L::vidx(k, 0) & ~1);
+    double a0 = 0, a1 = 0, a2 = 0, a3 = c.pcv[r] * x[L::IP];
     MPCB_UNROLL
-    for (int cc = 0; cc < 20; cc += 4) { a0 += G[cc] * xs[cc]; a1 += G[cc + 1] * xs[cc + 1]; a2 += G[cc + 2] * xs[cc + 2]; a3 += G[cc + 3] * xs[cc + 3]; }
-    a0 += G[20] * xs[20];
+    for (int cc = 0; cc < 24; cc += 4) {
+        const d2 g = ld2(G + cc), g2 = ld2(G + cc + 2), v = ld2(xs + cc), v2 = ld2(xs + cc + 2);
+        a0 += g.a * v.a; a1 += g.b * v.b; a2 += g2.a * v2.a; a3 += g2.b * v2.b;
+    }
     return (a0 + a1) + (a2 + a3);
 }
 // (A^T y)_i for variable (k, comp), i != p ; y in row order
 template <class SH>
 MPCB_DEV double col_times(const ACtx<SH>& c, int k, int comp, const double* y) {
     typedef AL<SH> L;
-    double g0 = 0, g1 = 0, g2 = 0, g3 = 0;
+    double g0 = 0, g1 = 0, g2_ = 0, g3 = 0;
     if (comp < 14) {
         const int s1 = k / 3, l1 = k - 3 * s1;
         if (k < SH::NN - 1) {
             const double* yy = y + 14 * (3 * s1) + comp;
-            g0 += c.D(0, l1) * yy[0]; g1 += c.D(1, l1) * yy[14]; g2 += c.D(2, l1) * yy[28];
+            g0 += c.D(0, l1) * yy[0]; g1 += c.D(1, l1) * yy[14]; g2_ += c.D(2, l1) * yy[28];
         }
         if (l1 == 0 && k > 0) {
             const double* yy = y + 14 * (3 * (s1 - 1)) + comp;
-            g0 += c.D(0, 3) * yy[0]; g1 += c.D(1, 3) * yy[14]; g2 += c.D(2, 3) * yy[28];
+            g0 += c.D(0, 3) * yy[0]; g1 += c.D(1, 3) * yy[14]; g2_ += c.D(2, 3) * yy[28];
         }
     }
     if (comp >= 7 && k < SH::NN - 1) g3 += c.mtp() * y[14 * k + comp - 7];
-    const double* G = c.Jg + k * L::JGS + comp;
+    const double* G = c.Gt + k * L::GTS + comp * L::GTC;
     const double* yi = y + SH::NEQ + 8 * k;
     MPCB_UNROLL
-    for (int rr = 0; rr < 8; rr += 4) { g0 += G[rr * 22] * yi[rr]; g1 += G[(rr + 1) * 22] * yi[rr + 1]; g2 += G[(rr + 2) * 22] * yi[rr + 2]; g3 += G[(rr + 3) * 22] * yi[rr + 3]; }
-    return (g0 + g1) + (g2 + g3);
+    for (int rr = 0; rr < 8; rr += 4) {
+        const d2 g = ld2(G + rr), g2 = ld2(G + rr + 2), v = ld2(yi + rr), v2 = ld2(yi + rr + 2);
+        g0 += g.a * v.a; g1 += g.b * v.b; g2_ += g2.a * v2.a; g3 += g2.b * v2.b;
+    }
+    return (g0 + g1) + (g2_ + g3);
 }
 // A[r, p]: equality rows from pcol, inequality rows from the last Jacobian column
 template <class SH>
 MPCB_DEV double pcoef(const ACtx<SH>& c, int r) {
     if (r < SH::NEQ) return c.pcol[r];
-    const int q = r - SH::NEQ;
-    return c.Jg[(q >> 3) * AL<SH>::JGS + (q & 7) * 22 + 21];
+    return c.pcv[r];
 }
 // Dot product of two vectors (length 416, zero padded) by the 32 lanes of warp `w`; returned on lane 0 (other lanes: junk).
 // Device: 13 strided products per lane + a 5-step shuffle butterfly.  The host emulation (lanes run one after the other)
@@ -650,9 +658,10 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
         MPCB_PROF(1)
         MPCB_PHASE({ b_ft(c, ts, tid); MPCB_WSTAMP(1) });
         MPCB_PROF(2)
-        // the separator right-hand side (71 threads, latency bound) shares its barrier interval with t = W rhs_I
-        MPCB_PHASE_NS(b_seprhs(c, tid));
+        // the separator right-hand side (71 threads, latency bound) shares its barrier interval with t = W rhs_I; it comes
+        // second because its threads own the short (32-coefficient) W rows, the 49-coefficient rows set the interval's length
         MPCB_PHASE_NS(b_w(c, ts, tid));
+        MPCB_PHASE_NS(b_seprhs(c, tid));
         MPCB_PHASE({
             const double o = MPCB_PEER(acc, 1);
             ts.t = wrole<SH>(tid).paired ? ts.acc + o : ts.acc;

@@ -67,9 +67,13 @@ MPCB_DEV void exp_fc(const Ctx<SH>& c, int tid, double* qb) {
             tm[(so + jj) * NT] = (cu >= 0 && col < SH::NB) ? -sym_packed<SH>(c.C, cu >> 2, col) : 0.0;
         }
     }
-    for (int e = tid; e < 19 * L::JGS + 1; e += NT) {
-        const int k = e / L::JGS, o = e - k * L::JGS;
-        img[L::I_JG + e] = (k < SH::NN && o < 176) ? c.Jg[k * 176 + o] : 0.0;
+    for (int e = tid; e < 19 * L::JGS; e += NT) {        // rows for A x, shifted by the parity of the node's first index
+        const int k = e / L::JGS, o = e - k * L::JGS, rr = o / L::JGR, cc = o - rr * L::JGR - (L::vidx(k, 0) & 1);
+        img[L::I_JG + e] = (cc >= 0 && cc < 21) ? c.Jg[k * 176 + rr * 22 + cc] : 0.0;
+    }
+    for (int e = tid; e < 19 * L::GTS; e += NT) {        // transposed for A^T y
+        const int k = e / L::GTS, o = e - k * L::GTS, comp = o / L::GTC, rr = o - comp * L::GTC;
+        img[L::I_GT + e] = rr < 8 ? c.Jg[k * 176 + rr * 22 + comp] : 0.0;
     }
 }
 // vectors: Hessian diagonal / arrow, A[:,p], D, row data, box data

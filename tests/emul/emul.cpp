@@ -108,8 +108,8 @@ int emul_kkt_apply(const mpcb_settings* st, const mpcb_limits* lim, const double
     }
     c.sc[0] = 0;        // no A^T w gather in this test: rhs is given directly
     MPCB_PHASE(b_ft(c, ts, tid));
-    MPCB_PHASE_NS(b_seprhs(c, tid));
     MPCB_PHASE_NS(b_w(c, ts, tid));
+    MPCB_PHASE_NS(b_seprhs(c, tid));
     MPCB_PHASE({ const double o = MPCB_PEER(acc, 1); ts.t = wrole<SH>(tid).paired ? ts.acc + o : ts.acc; });
     MPCB_PHASE_NS(c_separator(c, ts, tid));
     MPCB_PHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });

@@ -6,3 +6,6 @@ timeout 600 python bench.py --no-cpu-baseline > gpurun_out/${TAG}_bench.json 2> 
 python -c "
 import json;d=json.load(open('gpurun_out/${TAG}_bench.json'));print(d['value'],d['ms_per_step'],d['roofline']['frac'],d['roofline']['step'])"
 MPCB_LIB=mpc_motion_planner_b200/libmpcb_prof.so timeout 300 python tools/phase_profile.py 148 > gpurun_out/${TAG}_phase_cycles.txt 2>&1; cat gpurun_out/${TAG}_phase_cycles.txt
+if [ "$2" = "ncu" ]; then
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:admm -c 1 -o gpurun_out/${TAG}_admm python tools/run_small.py > gpurun_out/${TAG}_ncu.log 2>&1; echo "ncu full exit $?"
+fi

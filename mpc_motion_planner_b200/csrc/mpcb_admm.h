@@ -195,12 +195,31 @@ struct ATS {
 #endif
 };
 
+// The ADMM kernel runs its NT = 512 LOGICAL threads (the unit of every role map in this file) on ANT = 256 physical
+// threads: physical thread p executes logical threads p and p + 256 one after the other inside every phase.  A CTA of 256
+// threads may use 255 registers per thread, so each logical thread's phase body has ~90 registers for operands in flight
+// next to the 2 x 64 registers of W coefficients (with 512 physical threads it had ~45, which serialised every phase into
+// load -> use round trips, profiles/r1j_admm_kernel_hotlines.txt).  Logical warps w and w + 8 share physical warp w: same
+// lanes (shuffles are unchanged) and the same TMEM lane quadrant (w % 4).
+constexpr int ANT = NT / 2;
 #ifdef MPCB_EMUL
 #define MPCB_ADRV_PARAMS(SH) ACtx<SH>& c, ATS<SH>* tsv
 #define MPCB_ADRV_ARGS c, tsv
+#define MPCB_APHASE(...) MPCB_PHASE(__VA_ARGS__)
+#define MPCB_APHASE_NS(...) MPCB_PHASE_NS(__VA_ARGS__)
 #else
-#define MPCB_ADRV_PARAMS(SH) ACtx<SH>& c, ATS<SH>& ts, const int tid
-#define MPCB_ADRV_ARGS c, ts, tid
+#define MPCB_ADRV_PARAMS(SH) ACtx<SH>& c, ATS<SH>& ts0, ATS<SH>& ts1, const int ptid
+#define MPCB_ADRV_ARGS c, ts0, ts1, ptid
+#define MPCB_APHASE_NS(...)                                                   \
+    {                                                                         \
+        { const int tid = ptid; ATS<SH>& ts = ts0; (void)ts; (void)tid; __VA_ARGS__; }   \
+        { const int tid = ptid + ANT; ATS<SH>& ts = ts1; (void)ts; (void)tid; __VA_ARGS__; } \
+    }
+#define MPCB_APHASE(...)             \
+    {                                \
+        MPCB_APHASE_NS(__VA_ARGS__)  \
+        __syncthreads();             \
+    }
 #endif
 
 struct d2 { double a, b; };
@@ -648,37 +667,41 @@ MPCB_DEV void a_finish(ACtx<SH>& c, ATS<SH>& ts, int tid, int max_iter) {
 template <class SH>
 MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
     typedef AL<SH> L;
+#ifndef MPCB_EMUL
+    const int tid = ptid;            // for the profiling hooks outside the phases
+    (void)tid;
+#endif
     MPCB_PROF_DECL
-    MPCB_PHASE(a_load(c, ts, tid));
+    MPCB_APHASE(a_load(c, ts, tid));
     MPCB_PROF(0)
     const int max_iter = c.st->qp_max_iter, chk = c.st->qp_check_termination;
     for (int iter = 1; iter <= max_iter; iter++) {
         MPCB_WSTAMP(15)
-        MPCB_PHASE({ a_rhs(c, ts, tid); MPCB_WSTAMP(0) });
+        MPCB_APHASE({ a_rhs(c, ts, tid); MPCB_WSTAMP(0) });
         MPCB_PROF(1)
-        MPCB_PHASE({ b_ft(c, ts, tid); MPCB_WSTAMP(1) });
+        MPCB_APHASE({ b_ft(c, ts, tid); MPCB_WSTAMP(1) });
         MPCB_PROF(2)
         // the separator right-hand side (71 threads, latency bound) shares its barrier interval with t = W rhs_I; it comes
         // second because its threads own the short (32-coefficient) W rows, the 49-coefficient rows set the interval's length
-        MPCB_PHASE_NS(b_w(c, ts, tid));
-        MPCB_PHASE_NS(b_seprhs(c, tid));
-        MPCB_PHASE({
+        MPCB_APHASE_NS(b_w(c, ts, tid));
+        MPCB_APHASE_NS(b_seprhs(c, tid));
+        MPCB_APHASE({
             const double o = MPCB_PEER(acc, 1);
             ts.t = wrole<SH>(tid).paired ? ts.acc + o : ts.acc;
             MPCB_WSTAMP(2)
         });
         MPCB_PROF(3)
-        MPCB_PHASE_NS(c_separator(c, ts, tid));
-        MPCB_PHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
-        MPCB_PHASE({
+        MPCB_APHASE_NS(c_separator(c, ts, tid));
+        MPCB_APHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
+        MPCB_APHASE({
             const double s4 = ts.acc2 + MPCB_PEER(acc2, 2);
             const int cu = L::cunit(tid);
             if (cu >= 0 && (cu & 3) == 0) c.xt[L::sepidx(cu >> 2)] = s4;
             MPCB_WSTAMP(3)
         });
         MPCB_PROF(4)
-        MPCB_PHASE_NS(d_interior(c, ts, tid));
-        MPCB_PHASE({
+        MPCB_APHASE_NS(d_interior(c, ts, tid));
+        MPCB_APHASE({
             const double o = MPCB_PEER(acc, 1);
             const WRole r = wrole<SH>(tid);
             const double fx = r.paired ? ts.acc + o : ts.acc;
@@ -686,18 +709,18 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
             MPCB_WSTAMP(4)
         });
         MPCB_PROF(5)
-        MPCB_PHASE({ e_update(c, ts, tid); MPCB_WSTAMP(5) });
+        MPCB_APHASE({ e_update(c, ts, tid); MPCB_WSTAMP(5) });
         MPCB_WSTAMP(6)
         MPCB_PROF(6)
         if (chk > 0 && iter % chk == 0) {
-            MPCB_PHASE(chk_a(c, ts, tid));
-            MPCB_PHASE(chk_b(c, ts, tid));
-            MPCB_PHASE(chk_c(c, ts, tid, iter));
+            MPCB_APHASE(chk_a(c, ts, tid));
+            MPCB_APHASE(chk_b(c, ts, tid));
+            MPCB_APHASE(chk_c(c, ts, tid, iter));
             MPCB_PROF(7)
             if (c.isc[IS_QP_DONE]) break;
         }
     }
-    MPCB_PHASE(a_finish(c, ts, tid, max_iter));
+    MPCB_APHASE(a_finish(c, ts, tid, max_iter));
     MPCB_PROF(8)
 }
 

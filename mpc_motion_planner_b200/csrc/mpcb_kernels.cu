@@ -103,26 +103,31 @@ node_val_kernel(const int n, const int ntrial, const double tau, double* __restr
 
 // the hot kernel: <= qp_max_iter box-ADMM iterations of one QP per CTA at a time
 template <class SH>
-__global__ void __launch_bounds__(NT, 1)
+__global__ void __launch_bounds__(ANT, 1)
 admm_kernel(const __grid_constant__ KernelConst kc, const int n, int* __restrict__ counter, double* __restrict__ workspace, long long* prof) {
     extern __shared__ double smem[];
     __shared__ int s_next;
     __shared__ uint32_t s_tmem;
-    const int tid = threadIdx.x;
+    const int ptid = threadIdx.x;       // physical thread: runs the logical threads ptid and ptid + ANT (mpcb_admm.h)
     ACtx<SH> c;
     c.bind(smem);
     c.st = &kc.st;
     c.prof = prof;
-    ATS<SH> ts;
+    ATS<SH> ts0, ts1;
     // all 512 TMEM columns of the SM for this CTA (one CTA per SM): thread-private operand strips, mpcb_tmem.h
-    if (tid < 32) tm_alloc512(&s_tmem);
+    if (ptid < 32) tm_alloc512(&s_tmem);
     tm_fence_before();
     __syncthreads();
     tm_fence_after();
     const uint32_t tmem_base = s_tmem;
-    ts.tmaddr = tmem_base + ((uint32_t)(32 * ((tid >> 5) & 3)) << 16) + 2 * tm_warp_base(tid >> 5);
+    {
+        const int w0 = ptid >> 5, w1 = w0 + ANT / 32;      // logical warps; both sit in lane quadrant w0 % 4
+        const uint32_t lanes = (uint32_t)(32 * (w0 & 3)) << 16;
+        ts0.tmaddr = tmem_base + lanes + 2 * tm_warp_base(w0);
+        ts1.tmaddr = tmem_base + lanes + 2 * tm_warp_base(w1);
+    }
     for (;;) {
-        if (tid == 0) s_next = atomicAdd(counter, 1);
+        if (ptid == 0) s_next = atomicAdd(counter, 1);
         __syncthreads();
         const int i = s_next;
         __syncthreads();
@@ -130,11 +135,11 @@ admm_kernel(const __grid_constant__ KernelConst kc, const int n, int* __restrict
         double* ws = workspace + WS<SH>::STRIDE * i;
         if (reinterpret_cast<const int*>(ws + WS<SH>::FLAGS)[0]) continue;
         c.g = ws + WS<SH>::QB;
-        admm_run<SH>(c, ts, tid);
+        admm_run<SH>(c, ts0, ts1, ptid);
     }
     tm_fence_before();
     __syncthreads();
-    if (tid < 32) tm_free512(tmem_base);
+    if (ptid < 32) tm_free512(tmem_base);
 }
 
 // ---- read-out + accounting ------------------------------------------------------------------------------------------
@@ -259,7 +264,7 @@ cudaError_t launch_node_val(const KernelConst& kc, int n, double* workspace, cud
     return cudaGetLastError();
 }
 cudaError_t launch_admm(const KernelConst& kc, int n, int grid, int* counter, double* workspace, long long* prof, cudaStream_t stream) {
-    admm_kernel<SH36><<<grid, NT, AL<SH36>::BYTES, stream>>>(kc, n, counter, workspace, prof);
+    admm_kernel<SH36><<<grid, ANT, AL<SH36>::BYTES, stream>>>(kc, n, counter, workspace, prof);
     return cudaGetLastError();
 }
 cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double* su, const double* sT, const double* target, int npts,

@@ -36,6 +36,10 @@ W_IT = 2 * (18473 + 2 * 7679 + 5041 + 2 * 4856) + 6432   # one ADMM iteration: W
 W_FAC = 63 * 78 ** 2 + 4 * 49 * 78 ** 2 + 70 * 85 ** 2 + 71 ** 3 + 120000   # sweeps (interiors + separator) + assembly
 W_LIN = 300000                                            # 19 x (RNEA derivatives + CRBA + frame Jacobian) + collocation
 W_MERIT = 35000                                           # 19 x (RNEA + FK) + residuals
+# DRAM bytes of one admm_kernel launch per OCP, from the committed ncu --set full capture of this command
+# (profiles/r1l_admm_kernel_raw.csv: dram__bytes_read.sum 471.29 MB + dram__bytes_write.sum 11.08 MB for 1000 OCPs):
+# the factorised QP block (W, F, C^-1 strips and the Jacobian image, ~505 KB per OCP) is read once per QP.
+NCU_ADMM_DRAM_BYTES_PER_OCP = (471.291392e6 + 11.077376e6) / 1000
 
 
 def flops_of(stats):
@@ -99,7 +103,7 @@ def run_reference(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    n_sample = max(threads * 24, 48)
+    n_sample = max(threads * 64, 128)                    # about 2 s of CPU work per step on all host threads
     from oracle import oracle_py as O
     O.build()
     times = []
@@ -241,7 +245,8 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clk.summary(),
         "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak > 0 else None,
-                     "traffic": None, "peak_source": "FP64 FMA micro-benchmark run in this process (MEASURED_PEAKS.json has no FP64 figure)",
+                     "traffic": NCU_ADMM_DRAM_BYTES_PER_OCP * B, "traffic_source": "ncu --set full, profiles/r1l_admm_kernel_raw.csv (dram read + write of one admm_kernel launch, scaled to the batch)",
+                     "peak_source": "FP64 FMA micro-benchmark run in this process (MEASURED_PEAKS.json has no FP64 figure)",
                      "kernel": "admm_kernel", "flops_per_launch": flops_admm_launch, "kernel_ms": admm_ms_launch,
                      "kernel_share_of_step": sum(admm_ms) / ms_total,
                      "step": {"flops": flops_step, "ms": ms_total / args.steps, "achieved": achieved_step,
@@ -262,7 +267,7 @@ def run_ours(args):
     line["stats"]["p50_single_solve_latency_ms"] = float(sorted(lat)[len(lat) // 2])
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        n_sample = max(threads * 24, 48)
+        n_sample = max(threads * 320, 640)               # about 10 s of CPU work on all host threads
         v, dt = cpu_baseline(n_sample, threads)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"first {n_sample} OCPs of the same batch, {dt:.1f} s, oracle/ (CPU restatement; reference binary unbuildable here)"}

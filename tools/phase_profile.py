@@ -42,7 +42,7 @@ for k, nm in stage.items():
 print(f"  total                        {sum(out[k] for k in stage) / cta0_ocps:12.0f}")
 
 names2 = ["A rhs", "B1 F^T", "B2 W + sep rhs", "C separator", "D back-subst", "E update"]
-t0 = min(out[64 + 16 * 15 + w] for w in range(16))
+t0 = min(v for v in (out[64 + 16 * 15 + w] for w in range(16)) if v > 0)
 print("per-warp end-of-work times in iteration 100 of CTA 0 (cycles after the start of phase A; then the barrier):")
 for s_, nm in enumerate(names2):
     ends = [out[64 + 16 * s_ + w] - t0 for w in range(16)]

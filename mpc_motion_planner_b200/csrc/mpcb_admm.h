@@ -137,21 +137,18 @@ MPCB_HD FRole frole(int tid) {
     // warps 0..11: one (middle segment, chunk) per warp, lane = column (29 of 32 lanes); warps 12..15: chunk w - 12 of
     // segment 0 on lanes 0..14 and of segment 5 on lanes 16..30 -- every half-warp reads one F column stripe with an odd
     // stride (conflict-free) and broadcasts its rhs chunk
+    // (written with selects, not early returns: the ADMM phase that uses it is straight-line code)
     FRole f;
-    f.unit = -1; f.seg = 0; f.col = 0; f.r0 = 0; f.len = 0;
     const int w = tid >> 5, lane = tid & 31;
-    int ch;
-    if (w < 12) {
-        if (lane >= 29) return f;
-        f.seg = 1 + w / 3; ch = w % 3; f.col = lane;
-        f.r0 = ch == 0 ? 0 : (ch == 1 ? 18 : 34); f.len = ch == 0 ? 18 : (ch == 1 ? 16 : 15);
-    } else {
-        if ((lane & 15) == 15) return f;
-        ch = w - 12; f.col = lane & 15;
-        if (lane < 16) { f.seg = 0; f.r0 = 16 * ch; f.len = ch == 3 ? 15 : 16; }
-        else { f.seg = 5; f.r0 = 18 * ch; f.len = ch == 3 ? 16 : 18; }
-    }
-    f.unit = pfoff<SH>(f.seg) + ch * SH::nb(f.seg) + f.col;
+    const bool mid = w < 12, lo = lane < 16;
+    const int ch = mid ? w % 3 : w - 12;
+    f.seg = mid ? 1 + w / 3 : (lo ? 0 : 5);
+    f.col = mid ? lane : (lane & 15);
+    f.r0 = mid ? (ch == 0 ? 0 : (ch == 1 ? 18 : 34)) : (lo ? 16 * ch : 18 * ch);
+    f.len = mid ? (ch == 0 ? 18 : (ch == 1 ? 16 : 15)) : (lo ? (ch == 3 ? 15 : 16) : (ch == 3 ? 16 : 18));
+    const bool valid = mid ? lane < 29 : (lane & 15) != 15;
+    f.unit = valid ? pfoff<SH>(f.seg) + ch * SH::nb(f.seg) + f.col : -1;
+    if (!valid) { f.len = 0; }
     return f;
 }
 
@@ -374,14 +371,45 @@ MPCB_DEV void a_load(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 }
 
 // ---- phase A: rhs = sigma x - h + rho_b z_b - y_b + A^T w ;  warp 13 folds the products A[r,p] w_r into 32 partial sums ----
+// Straight-line (branch-free) so that the compiler can interleave the loads of the two logical threads a physical thread
+// runs: conditions become zero coefficients (dt[20] holds 0.0) and clamped addresses, the store is predicated.
 template <class SH>
 MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid) {
-    int i, k, comp;
-    if (vrole<SH>(tid, i, k, comp)) {
-        const double g = (k >= 0) ? col_times(c, k, comp, c.w) : 0.0;     // p: the gather arrives through sc[0] in phase B2
-        const double h = (k < 0) ? 1.0 : 0.0;              // gradient of the Mayer cost p (robot_ocp.hpp:206)
-        c.rhs[i] = c.st->qp_sigma * ts.x - h + ts.rhoB * ts.zB - ts.yB + g;
-    }
+    typedef AL<SH> L;
+    const bool isp = tid == L::PTID;
+    const int ii = tid < L::IP ? tid : 0;
+    const int s = (ii / L::SEG) > 5 ? 5 : (ii / L::SEG), rem = ii - L::SEG * s;
+    const int j = rem / 21, comp = rem - 21 * j, k = 3 * s + j;        // pads of segments 0..4 decode to (k = 3 s + 3, comp < 3): valid addresses
+    const bool valid = (tid < L::IP) && !(s < 5 && rem >= 63);
+    const double* y = c.w;
+    const int s1 = k / 3, l1 = k - 3 * s1;
+    const bool st = comp < 14;
+    const bool c1 = st && k < SH::NN - 1, c2 = st && l1 == 0 && k > 0, c3 = comp >= 7 && k < SH::NN - 1;
+    const int cc = st ? comp : 0, Z = 20;
+    const double* yy1 = y + 42 * (c1 ? s1 : 0) + cc;
+    const double* yy2 = y + 42 * (c2 ? s1 - 1 : 0) + cc;
+    const double* y3 = y + (c3 ? 14 * k + comp - 7 : 0);
+    const double d10 = c.dt[c1 ? l1 : Z], d11 = c.dt[c1 ? 4 + l1 : Z], d12 = c.dt[c1 ? 8 + l1 : Z];
+    const double d20 = c.dt[c2 ? 3 : Z], d21 = c.dt[c2 ? 7 : Z], d22 = c.dt[c2 ? 11 : Z];
+    const double mt = c.dt[c3 ? 16 : Z];
+    const double* G = c.Gt + k * L::GTS + comp * L::GTC;
+    const double* yi = y + SH::NEQ + 8 * k;
+    const d2 ga = ld2(G), gb = ld2(G + 2), gc = ld2(G + 4), gd = ld2(G + 6);
+    const d2 va = ld2(yi), vb = ld2(yi + 2), vc = ld2(yi + 4), vd = ld2(yi + 6);
+    double g0 = 0, g1 = 0, g2 = 0, g3 = 0;
+    g0 += d10 * yy1[0]; g1 += d11 * yy1[14]; g2 += d12 * yy1[28];
+    g0 += d20 * yy2[0]; g1 += d21 * yy2[14]; g2 += d22 * yy2[28];
+    g3 += mt * y3[0];
+    g0 += ga.a * va.a; g1 += ga.b * va.b; g2 += gb.a * vb.a; g3 += gb.b * vb.b;
+    g0 += gc.a * vc.a; g1 += gc.b * vc.b; g2 += gd.a * vd.a; g3 += gd.b * vd.b;
+    const double g = isp ? 0.0 : (g0 + g1) + (g2 + g3);              // p: the gather arrives through sc[0] in phase B2
+    const double h = isp ? 1.0 : 0.0;                                  // gradient of the Mayer cost p (robot_ocp.hpp:206)
+    const double r = c.st->qp_sigma * ts.x - h + ts.rhoB * ts.zB - ts.yB + g;
+    if (valid || isp) c.rhs[isp ? L::IP : tid] = r;
+}
+// warp 13 folds the products A[r,p] w_r into (A^T w)_p
+template <class SH>
+MPCB_DEV void a_rhs_p(ACtx<SH>& c, int tid) {
     double s;
     if (warp_vdot<SH>(tid, 13, c.pcv, c.w, c.psum, s)) c.sc[0] = s;       // (A^T w)_p = sum_r A[r,p] w_r
 }
@@ -398,7 +426,7 @@ MPCB_DEV void b_ft(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     const int so = L::tm_ft(tid);
     tm_ld(ts.tma(), so, f0); tm_ld(ts.tma(), so + 8, f1); tm_ld(ts.tma(), so + 16, f2);
     tm_wait(f0, f1, f2);
-    if (f.unit >= 0 && f.col < SH::nb(f.seg) - 1) {       // the p column is summed through fpv (phase A) instead
+    {
         const double* b = c.rhs + L::ibase(f.seg) + f.r0;
         double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
         MPCB_UNROLL
@@ -412,7 +440,8 @@ MPCB_DEV void b_ft(ACtx<SH>& c, ATS<SH>& ts, int tid) {
             a0 += f1.get(i) * v.a; a1 += f1.get(i + 1) * v.b; a2 += f1.get(i + 2) * v2.a; a3 += f1.get(i + 3) * v2.b;
         }
         { const d2 v = ld2(b + 16); a0 += f2.get(0) * v.a; a1 += f2.get(1) * v.b; }
-        c.partF[f.unit] = (a0 + a1) + (a2 + a3);
+        // the p column is summed through fpc (phase B') instead
+        if (f.unit >= 0 && f.col < SH::nb(f.seg) - 1) c.partF[f.unit] = (a0 + a1) + (a2 + a3);
     }
 }
 // ---- phase B2: t = W rhs_I from the register-resident rows (runs in the same barrier interval as the separator rhs) ---
@@ -677,7 +706,8 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
     const int max_iter = c.st->qp_max_iter, chk = c.st->qp_check_termination;
     for (int iter = 1; iter <= max_iter; iter++) {
         MPCB_WSTAMP(15)
-        MPCB_APHASE({ a_rhs(c, ts, tid); MPCB_WSTAMP(0) });
+        MPCB_APHASE_NS(a_rhs(c, ts, tid));
+        MPCB_APHASE({ a_rhs_p(c, tid); MPCB_WSTAMP(0) });
         MPCB_PROF(1)
         MPCB_APHASE({ b_ft(c, ts, tid); MPCB_WSTAMP(1) });
         MPCB_PROF(2)

@@ -6,8 +6,9 @@
 //   * fixed-size vectors are mpcb::Vec<N> (std::array based) instead of Eigen::Matrix<double,N,1>; trajectories are
 //     mpcb::Traj<ROWS> (column = sample) -- Eigen is not available in this environment;
 //   * the solver runs on the GPU (no CPU path): the constructor throws std::runtime_error if no CUDA device is found;
-//   * the Ruckig warm start is replaced by a cubic-Hermite joint profile (ruckig is absent):
-//     warm_start_RK() / get_ruckig_trajectory() / get_RK_point() keep their names and operate on that profile;
+//   * the Ruckig warm start is our own jerk-limited synchronised generator (csrc/mpcb_otg.h; ruckig itself is absent,
+//     SURVEY.md 8f-N1; pinned on the Ruckig trajectory the reference embeds): warm_start_RK() /
+//     get_ruckig_trajectory() / get_RK_point() keep their names and operate on that profile;
 //   * bounds: initial pin and final box are always applied last; get_MPC_point clamps to t = T (Q9);
 //     set_min_height does not print (Q10); random numbers come from a seeded counter RNG (Q13);
 //   * solve_batch() is the batched entry the reference does not have.
@@ -200,8 +201,14 @@ class MotionPlanner {
         interpolate(s, q, v, a);
         tau = robot.rnea(q, v, a);
     }
-    // motionPlanner.hpp:130-142
+    // motionPlanner.hpp:130-142: the synchronised jerk-limited profile at time t (Trajectory::at_time); before the first
+    // warm start, or for a problem the generator rejected, the cubic-Hermite fallback of mpcb_guess_batch
     void get_RK_point(double t, Vec7& q, Vec7& v, Vec7& a, Vec7& tau) const {
+        if (rk_ok_) {
+            mpcb_otg_at_time(&rk_traj_, std::fmin(std::fmax(t, 0.0), rk_T_), q.data(), v.data(), a.data());
+            tau = robot.rnea(q, v, a);
+            return;
+        }
         const double T = rk_T_, s = T > 0 ? std::fmin(std::fmax(t / T, 0.0), 1.0) : 0.0;
         const double h00 = 2 * s * s * s - 3 * s * s + 1, h10 = s * s * s - 2 * s * s + s, h01 = -2 * s * s * s + 3 * s * s, h11 = s * s * s - s * s;
         const double d00 = 6 * s * s - 6 * s, d10 = 3 * s * s - 4 * s + 1, d01 = -6 * s * s + 6 * s, d11 = 3 * s * s - 2 * s;
@@ -240,10 +247,11 @@ class MotionPlanner {
     int num_nodes() const { return N_; }
 
   private:
-    // motionPlanner.cpp:146-175 with the cubic-Hermite stand-in for Ruckig
+    // motionPlanner.cpp:146-175: otg.calculate + sampling at the node times (mpcb_guess_batch does both)
     void warm_start_RK() {
         mpcb_guess_batch(&settings_, &limits_, 1, current_state.data(), target_state.data(), x_guess_.data(), u_guess_.data(), &p_guess_);
         rk_T_ = p_guess_; rk_x0_ = current_state; rk_xT_ = target_state;
+        rk_ok_ = mpcb_otg_calculate(&limits_, current_state.data(), target_state.data(), &rk_traj_) >= 0 && rk_traj_.T == p_guess_;
     }
     // polympc solution_x_at / solution_u_at: Lagrange interpolation on the segment containing s in [0,1]
     void interpolate(double s, Vec7& q, Vec7& v, Vec7& a) const {
@@ -277,6 +285,8 @@ class MotionPlanner {
     int N_ = 0;
     std::vector<double> nodes_, x_guess_, u_guess_, sol_x_, sol_u_, lam_;
     double p_guess_ = 1.0, sol_T_ = 0.0, rk_T_ = 1.0;
+    mpcb_otg_traj rk_traj_{};
+    bool rk_ok_ = false;
     State rk_x0_, rk_xT_;
     bool carry_duals_ = false;
     unsigned long long seed_ = 0, stream_ = 0;

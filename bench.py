@@ -239,7 +239,7 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": int(total_ocps), "seed": 1, "guess": "jerk-limited synchronised profile (csrc/mpcb_otg.h, Ruckig's role; pinned on the reference-embedded Ruckig trajectory)",
+        "config": {"workload": WORKLOAD if B == 1000 else WORKLOAD.replace("1000 random", f"{B} random").replace("mpc_benchmark:", "mpc_benchmark generator, larger batch (BASELINE config 3):"), "batch_per_gpu": B, "global_batch": int(total_ocps), "seed": 1, "guess": "jerk-limited synchronised profile (csrc/mpcb_otg.h, Ruckig's role; pinned on the reference-embedded Ruckig trajectory)",
                    "l2": "256 MiB buffer written between timed steps (L2 flush)", "parallelism": f"batch shards x{world}, stats all_gather"},
         "e2e": {"value": total_ocps / t_e2e_max, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": e2e_steps},
         "gpu_launches": int(launches),

@@ -452,6 +452,17 @@ MPCB_DEV void b_ft(ACtx<SH>& c, ATS<SH>& ts, int tid) {
         if (f.unit >= 0 && f.col < SH::nb(f.seg) - 1) c.partF[f.unit] = (a0 + a1) + (a2 + a3);
     }
     if (tid == 31) c.sc[0] = tree32(c.psum);        // (A^T w)_p from the partial sums of phase A (a_rhs_p); lane 31 of warp 0 has no unit
+    if ((tid >> 5) == 15) {
+        // (F^T rhs_I)_p = sum_i F[i,p] rhs_i: 32 strided partial sums here, added up by the thread that forms r_B[p] in the
+        // next interval (b_seprhs) -- the same split as for (A^T w)_p, again to keep a shuffle butterfly off the longest path
+        const double* p = c.fpc + (tid & 31);
+        const double* q = c.rhs + (tid & 31);
+        double a0 = p[0] * q[0], a1 = p[32] * q[32], a2 = p[64] * q[64], a3 = p[96] * q[96];
+        a0 += p[128] * q[128]; a1 += p[160] * q[160]; a2 += p[192] * q[192]; a3 += p[224] * q[224];
+        a0 += p[256] * q[256]; a1 += p[288] * q[288]; a2 += p[320] * q[320]; a3 += p[352] * q[352];
+        a0 += p[384] * q[384];
+        c.psum[32 + (tid & 31)] = (a0 + a1) + (a2 + a3);
+    }
 }
 // ---- phase B2: t = W rhs_I from the register-resident rows (runs in the same barrier interval as the separator rhs) ---
 template <class SH>
@@ -506,9 +517,8 @@ MPCB_DEV void b_w(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 template <class SH>
 MPCB_DEV void b_seprhs(ACtx<SH>& c, int tid) {
     typedef AL<SH> L;
-    {   // p: r_B[p] = rhs_p + (A^T w)_p - (F^T rhs_I)_p ; the second dot product over all interior variables by warp 15
-        double s;
-        if (warp_vdot<SH>(tid, 15, c.fpc, c.rhs, c.psum + 32, s)) c.rB[SH::NB - 1] = (c.rhs[L::IP] + c.sc[0]) - s;
+    {   // p: r_B[p] = rhs_p + (A^T w)_p - (F^T rhs_I)_p ; both dot products arrive as sums from phase B1
+        if (tid == 15 * 32) c.rB[SH::NB - 1] = (c.rhs[L::IP] + c.sc[0]) - tree32(c.psum + 32);
     }
     if (tid >= SH::NB - 1) return;
     const int sj = tid / 14 + 1, cc = tid - 14 * (sj - 1);     // junction x_{3 sj}: right boundary of segment sj-1, left of sj

@@ -84,6 +84,14 @@ class PandaWrapper {
         mpcb_forward_velocities(q.data(), qdot.data(), t.data());
         return t;
     }
+    // pandaWrapper.cpp:14-58 (orientation column-major 3 x 3 as Eigen::Matrix3d::data(); random start seeded by `seed`)
+    Vec7 inverse_kinematic(const std::array<double, 9>& orientation, const Vec3& position, unsigned long long seed = 0) const {
+        mpcb_limits l;
+        mpcb_default_limits(&l);
+        Vec7 q;
+        mpcb_inverse_kinematic(&l, orientation.data(), position.data(), seed, q.data(), nullptr);
+        return q;
+    }
     Vec7 rnea(const Vec7& q, const Vec7& v, const Vec7& a) const { Vec7 tau; mpcb_rnea(q.data(), v.data(), a.data(), tau.data()); return tau; }
     double tool_height(const Vec7& q) const { double z; mpcb_frame_height(q.data(), 1, &z); return z; }      // oMf[panda_tool].z
     double joint7_height(const Vec7& q) const { double z; mpcb_frame_height(q.data(), 0, &z); return z; }    // oMi[7].z

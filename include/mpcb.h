@@ -192,6 +192,12 @@ int mpcb_sample_random_state(const mpcb_limits* lim, unsigned long long seed, un
 int mpcb_forward_velocities(const double* q, const double* qd, double* task6);
 int mpcb_inverse_velocities(const double* q, const double* linear3, const double* angular3, double* qd);
 int mpcb_rnea(const double* q, const double* v, const double* a, double* tau);
+/*   mpcb_tool_pose            oMf[panda_tool] after forwardKinematics + updateFramePlacement (examples/benchmark.cpp:108-110):
+ *                             rotation column-major (Eigen Matrix3d::data()) and position
+ *   mpcb_inverse_kinematic    PandaWrapper::inverse_kinematic (robot_utils/pandaWrapper.cpp:14-58): damped closed-loop IK of the
+ *                             tool frame from a random configuration (seeded); 0 = converged, 1 = iteration limit */
+int mpcb_tool_pose(const double* q, double* R_colmajor, double* pos);
+int mpcb_inverse_kinematic(const mpcb_limits* lim, const double* R_des_colmajor, const double* p_des, unsigned long long seed, double* q_out, int* iters);
 int mpcb_frame_height(const double* q, int frame, double* z);
 
 #ifdef __cplusplus

@@ -153,6 +153,82 @@ int mpcb_inverse_velocities(const double* q, const double* linear3, const double
     inverse_velocities(q, task, qd);
     return MPCB_OK;
 }
+// oMf[panda_tool] (pinocchio::forwardKinematics + updateFramePlacement, examples/benchmark.cpp:108-110): rotation (column-major,
+// as Eigen's Matrix3d::data()) and position.  panda_joint8 / panda_tool carry no rotation (panda_arm.urdf:134-152).
+int mpcb_tool_pose(const double* q, double* R_colmajor, double* pos) {
+    if (!q || !R_colmajor || !pos) return MPCB_ERR_BAD_ARG;
+    double oR[7][9], op[7][3];
+    rbd::fk_world(q, oR, op);
+    rbd::frame_jacobian(oR, op, PANDA(PANDA_TOOL_OFFSET), nullptr, pos);
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) R_colmajor[3 * c + r] = oR[6][3 * r + c];
+    return MPCB_OK;
+}
+// PandaWrapper::inverse_kinematic (robot_utils/pandaWrapper.cpp:14-58): damped closed-loop inverse kinematics of the tool
+// frame from a random configuration; eps 1e-4, <= 1000 iterations, step 0.1, damping 1e-2; the error is log6 of
+// oMdes^-1 oMf (linear part first), the Jacobian is the LOCAL frame Jacobian, exactly as the reference does.
+// Returns 0 when converged, 1 when the iteration limit was hit (the reference returns q in both cases).
+int mpcb_inverse_kinematic(const mpcb_limits* lim, const double* R_des_colmajor, const double* p_des, unsigned long long seed, double* q_out, int* iters) {
+    if (!lim || !R_des_colmajor || !p_des || !q_out) return MPCB_ERR_BAD_ARG;
+    Rng rng(seed, 0x1C);
+    double q[7], Rd[9];
+    for (int j = 0; j < 7; j++) q[j] = 0.5 * (lim->qmin[j] + lim->qmax[j]) + 0.5 * rng.sym() * (lim->qmax[j] - lim->qmin[j]);   // randomConfiguration
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) Rd[3 * r + c] = R_des_colmajor[3 * c + r];
+    int rc = 1, i = 0;
+    for (;; i++) {
+        double oR[7][9], op[7][3], Jw[42], pf[3];
+        rbd::fk_world(q, oR, op);
+        rbd::frame_jacobian(oR, op, PANDA(PANDA_TOOL_OFFSET), Jw, pf);
+        const double* Rf = oR[6];
+        double dR[9], dp[3], d[3] = {pf[0] - p_des[0], pf[1] - p_des[1], pf[2] - p_des[2]};
+        for (int r = 0; r < 3; r++) {
+            dp[r] = Rd[r] * d[0] + Rd[3 + r] * d[1] + Rd[6 + r] * d[2];
+            for (int c = 0; c < 3; c++) dR[3 * r + c] = Rd[r] * Rf[c] + Rd[3 + r] * Rf[3 + c] + Rd[6 + r] * Rf[6 + c];
+        }
+        // log6
+        double w[3] = {0.5 * (dR[7] - dR[5]), 0.5 * (dR[2] - dR[6]), 0.5 * (dR[3] - dR[1])};
+        double ct = 0.5 * (dR[0] + dR[4] + dR[8] - 1.0);
+        ct = ct > 1 ? 1 : (ct < -1 ? -1 : ct);
+        const double th = acos(ct), st = sqrt(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+        const double sc = th < 1e-8 ? 1.0 : (st > 1e-12 ? th / st : 0.0);
+        for (int k = 0; k < 3; k++) w[k] *= sc;
+        const double beta = th < 1e-4 ? 1.0 / 12.0 : (1.0 - th * sin(th) / (2.0 * (1.0 - ct))) / (th * th);
+        double wxp[3] = {w[1] * dp[2] - w[2] * dp[1], w[2] * dp[0] - w[0] * dp[2], w[0] * dp[1] - w[1] * dp[0]};
+        double wxwxp[3] = {w[1] * wxp[2] - w[2] * wxp[1], w[2] * wxp[0] - w[0] * wxp[2], w[0] * wxp[1] - w[1] * wxp[0]};
+        double err[6];
+        for (int k = 0; k < 3; k++) { err[k] = dp[k] - 0.5 * wxp[k] + beta * wxwxp[k]; err[3 + k] = w[k]; }
+        double en = 0;
+        for (int k = 0; k < 6; k++) en += err[k] * err[k];
+        if (sqrt(en) < 1e-4) { rc = 0; break; }
+        if (i >= 1000) break;
+        // LOCAL frame Jacobian = blockdiag(Rf^T, Rf^T) x world-aligned Jacobian
+        double J[42], A[36], Lm[36], D[6], y[6];
+        for (int j = 0; j < 7; j++)
+            for (int r = 0; r < 3; r++) {
+                J[r * 7 + j] = Rf[r] * Jw[j] + Rf[3 + r] * Jw[7 + j] + Rf[6 + r] * Jw[14 + j];
+                J[(3 + r) * 7 + j] = Rf[r] * Jw[21 + j] + Rf[3 + r] * Jw[28 + j] + Rf[6 + r] * Jw[35 + j];
+            }
+        for (int r = 0; r < 6; r++)
+            for (int c = 0; c < 6; c++) { double s2 = 0; for (int j = 0; j < 7; j++) s2 += J[r * 7 + j] * J[c * 7 + j]; A[r * 6 + c] = s2 + (r == c ? 1e-2 : 0.0); }
+        memset(Lm, 0, sizeof Lm);
+        for (int j = 0; j < 6; j++) {
+            double dd = A[j * 6 + j];
+            for (int k = 0; k < j; k++) dd -= Lm[j * 6 + k] * Lm[j * 6 + k] * D[k];
+            D[j] = dd; Lm[j * 6 + j] = 1;
+            for (int r = j + 1; r < 6; r++) {
+                double s2 = A[r * 6 + j];
+                for (int k = 0; k < j; k++) s2 -= Lm[r * 6 + k] * Lm[j * 6 + k] * D[k];
+                Lm[r * 6 + j] = s2 / dd;
+            }
+        }
+        for (int r = 0; r < 6; r++) { double s2 = err[r]; for (int k = 0; k < r; k++) s2 -= Lm[r * 6 + k] * y[k]; y[r] = s2; }
+        for (int r = 0; r < 6; r++) y[r] /= D[r];
+        for (int r = 5; r >= 0; r--) { double s2 = y[r]; for (int k = r + 1; k < 6; k++) s2 -= Lm[k * 6 + r] * y[k]; y[r] = s2; }
+        for (int j = 0; j < 7; j++) { double s2 = 0; for (int r = 0; r < 6; r++) s2 += J[r * 7 + j] * y[r]; q[j] -= 0.1 * s2; }
+    }
+    for (int j = 0; j < 7; j++) q_out[j] = q[j];
+    if (iters) *iters = i;
+    return rc;
+}
 int mpcb_rnea(const double* q, const double* v, const double* a, double* tau) {
     if (!q || !v || !a || !tau) return MPCB_ERR_BAD_ARG;
     double g[8];

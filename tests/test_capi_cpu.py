@@ -90,3 +90,33 @@ def test_guess_respects_margins_and_endpoints():
     assert ok.sum() >= 45
     assert (np.abs(gx[ok][:, :, 7:]) <= 0.8 * np.array(lim.vmax) + 1e-9).all()
     assert (np.abs(gu[ok]) <= 0.6 * np.array(lim.amax) + 1e-9).all()
+
+
+def test_tool_pose_and_inverse_kinematic():
+    """PandaWrapper::inverse_kinematic (robot_utils/pandaWrapper.cpp:14-58) and the FK frame placement it iterates on: the
+    pose of a random configuration is reached again (tolerance 1e-4 on log6, i.e. ~1e-4 on rotation entries and position)
+    whenever the reference's 1000-iteration budget suffices."""
+    import ctypes as C
+    import numpy as np
+    import mpc_motion_planner_b200 as M
+    L = M.load_library(); lim = M.default_limits([0.8, 0.8, 0.6, 0.9, 0.1])
+
+    def pose(q):
+        R = np.zeros(9); p = np.zeros(3)
+        assert L.mpcb_tool_pose(q.ctypes.data_as(C.c_void_p), R.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p)) == 0
+        return R, p
+
+    rng = np.random.default_rng(0); converged = 0
+    for t in range(10):
+        qs = np.array(lim.qmin) + rng.random(7) * (np.array(lim.qmax) - np.array(lim.qmin))
+        R, p = pose(qs)
+        assert abs(np.linalg.det(R.reshape(3, 3)) - 1) < 1e-12
+        q = np.zeros(7); it = C.c_int()
+        rc = L.mpcb_inverse_kinematic(C.byref(lim), R.ctypes.data_as(C.c_void_p), p.ctypes.data_as(C.c_void_p), C.c_ulonglong(t),
+                                      q.ctypes.data_as(C.c_void_p), C.byref(it))
+        assert rc in (0, 1) and 0 <= it.value <= 1000
+        if rc == 0:
+            R2, p2 = pose(q)
+            assert np.abs(R2 - R).max() < 2e-4 and np.abs(p2 - p).max() < 2e-4
+            converged += 1
+    assert converged >= 6

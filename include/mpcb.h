@@ -182,6 +182,13 @@ int mpcb_otg_at_time(const mpcb_otg_traj* traj, double t, double* q, double* v, 
 int mpcb_guess_batch(const mpcb_settings* s, const mpcb_limits* lim, int n, const double* x0, const double* xT,
                      double* guess_x, double* guess_u, double* guess_T);
 
+/* The same warm start computed on the device of handle `h` with its current limits (otg_guess_kernel: 8 lanes per problem, one
+ * joint per lane), so that a batch can be generated, warm-started and solved without the host touching it.  `mem` says whether the
+ * five arrays are host or device pointers.  Same per-joint routines as mpcb_guess_batch; results agree to rounding (the device
+ * contracts multiply-adds). */
+int mpcb_guess_batch_gpu(mpcb_handle* h, int n, const double* x0, const double* xT, double* guess_x, double* guess_u, double* guess_T,
+                         int mem, void* cuda_stream);
+
 /* Single-state host helpers used by the C++ MotionPlanner mirror (include/motion_planner.hpp):
  *   mpcb_sample_random_state  MotionPlanner::sample_random_state (motionPlanner.cpp:102-114), counter-based RNG (seed, stream)
  *   mpcb_forward_velocities   PandaWrapper::forward_velocities (robot_utils/pandaWrapper.cpp:90-107): tool twist [lin; ang]

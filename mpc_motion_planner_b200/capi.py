@@ -218,6 +218,21 @@ class Solver:
                                      C.c_void_p(stream) if stream else None)
         self._check(rc, "mpcb_solve_batch")
 
+    def guess(self, x0, xT):
+        """warm_start_RK for a batch on the device (mpcb_guess_batch_gpu, host arrays in and out)."""
+        x0 = _d(np.atleast_2d(x0)); xT = _d(np.atleast_2d(xT))
+        n = x0.shape[0]
+        gx = np.zeros((n, 14 * self.N)); gu = np.zeros((n, 7 * self.N)); gT = np.zeros(n)
+        rc = self.L.mpcb_guess_batch_gpu(self.h, C.c_int(n), _p(x0), _p(xT), _p(gx), _p(gu), _p(gT), C.c_int(MEM_HOST), None)
+        self._check(rc, "mpcb_guess_batch_gpu")
+        return gx, gu, gT
+
+    def guess_device(self, n, x0, xT, gx, gu, gT, stream=0):
+        """Device-pointer form (raw addresses); only enqueues the kernel."""
+        rc = self.L.mpcb_guess_batch_gpu(self.h, C.c_int(n), _p(x0), _p(xT), _p(gx), _p(gu), _p(gT), C.c_int(MEM_DEVICE),
+                                         C.c_void_p(stream) if stream else None)
+        self._check(rc, "mpcb_guess_batch_gpu")
+
     def sample(self, sx, su, sT, target=None, npts=200, want_traj=True, want_acc=True):
         sx = _d(np.atleast_2d(sx)); su = _d(np.atleast_2d(su)); sT = _d(np.atleast_1d(sT))
         n = sT.shape[0]

@@ -294,6 +294,46 @@ int mpcb_sample_batch(mpcb_handle* h, int n, const double* sol_x, const double* 
     return MPCB_OK;
 }
 
+int mpcb_guess_batch_gpu(mpcb_handle* h, int n, const double* x0, const double* xT, double* gx, double* gu, double* gT, int mem, void* stream_) {
+    if (!h) return MPCB_ERR_BAD_ARG;
+    if (n < 0 || (n > 0 && (!x0 || !xT || !gx || !gu || !gT))) { h->err = "bad argument"; return MPCB_ERR_BAD_ARG; }
+    if (mem != MPCB_MEM_HOST && mem != MPCB_MEM_DEVICE) { h->err = "mem must be MPCB_MEM_HOST or MPCB_MEM_DEVICE"; return MPCB_ERR_BAD_ARG; }
+    if (n == 0) return MPCB_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CK(cudaSetDevice(h->device));
+    OtgConst oc;
+    oc.N = mpcb_num_nodes(&h->st);
+    if (oc.N > 64 || mpcb_time_nodes(&h->st, oc.tn) != MPCB_OK) { h->err = "unsupported number of nodes"; return MPCB_ERR_UNSUPPORTED; }
+    for (int d = 0; d < 7; d++) {
+        oc.vl[d] = h->lim.margins[1] * h->lim.vmax[d]; oc.al[d] = h->lim.margins[2] * h->lim.amax[d]; oc.jl[d] = h->lim.margins[4] * h->lim.jmax[d];
+    }
+    oc.p_ub = h->lim.p_ub;
+    const int N = oc.N;
+    const size_t b14 = sizeof(double) * 14 * n, bgx = sizeof(double) * 14 * N * n, bgu = sizeof(double) * 7 * N * n, bT = sizeof(double) * n;
+    const double *dx0 = x0, *dxT = xT;
+    double *dgx = gx, *dgu = gu, *dgT = gT;
+    if (mem == MPCB_MEM_HOST) {
+        int rc = ensure_stage(h, 2 * al(b14) + al(bgx) + al(bgu) + al(bT));
+        if (rc) return rc;
+        char* p = (char*)h->d_stage;
+        auto take = [&](size_t b) { char* r = p; p += al(b); return r; };
+        double* a = (double*)take(b14); double* b = (double*)take(b14);
+        dgx = (double*)take(bgx); dgu = (double*)take(bgu); dgT = (double*)take(bT);
+        CK(cudaMemcpyAsync(a, x0, b14, cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(b, xT, b14, cudaMemcpyHostToDevice, stream));
+        dx0 = a; dxT = b;
+    }
+    CK(launch_otg_guess(oc, n, dx0, dxT, dgx, dgu, dgT, stream));
+    h->launches += 1;
+    if (mem == MPCB_MEM_HOST) {
+        CK(cudaMemcpyAsync(gx, dgx, bgx, cudaMemcpyDeviceToHost, stream));
+        CK(cudaMemcpyAsync(gu, dgu, bgu, cudaMemcpyDeviceToHost, stream));
+        CK(cudaMemcpyAsync(gT, dgT, bT, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+    }
+    return MPCB_OK;
+}
+
 double mpcb_last_solve_ms(mpcb_handle* h) {
     if (!h || !h->timed) return -1.0;
     cudaSetDevice(h->device);

@@ -11,6 +11,7 @@
 #include <stdint.h>
 
 #include "mpcb_kernels.h"
+#include "mpcb_otg.h"
 #include "mpcb_sqp.h"
 
 namespace mpcb {
@@ -225,6 +226,78 @@ sample_kernel(const __grid_constant__ KernelConst kc, const double* __restrict__
     }
 }
 
+// ---- warm start (MotionPlanner::warm_start_RK, /root/reference/mpc_solver/motionPlanner.cpp:146-175) ---------------------------
+// 8 lanes per problem, lane d < 7 owns joint d (lane 7 idles): step 1 per lane, max over the group, step 2 per lane, retry with
+// a longer T while any joint sits in a blocked interval, then every lane samples its joint at the node times.  The per-joint
+// routines are the ones the host path uses (csrc/mpcb_otg.h), so both paths take the same decisions.
+constexpr int OTG_NT = 128;
+__global__ void __launch_bounds__(OTG_NT)
+otg_guess_kernel(const __grid_constant__ OtgConst oc, const int n, const double* __restrict__ x0, const double* __restrict__ xT,
+                 double* __restrict__ gx, double* __restrict__ gu, double* __restrict__ gT) {
+    const int gt = blockIdx.x * OTG_NT + threadIdx.x, i = gt >> 3, d = gt & 7, lane = threadIdx.x & 31;
+    if (i >= n) return;                                   // whole groups leave together
+    const unsigned gmask = 0xFFu << (lane & 24);
+    const bool act = d < 7;
+    const int dd = act ? d : 0;
+    const double q0 = x0[(size_t)14 * i + dd], v0 = x0[(size_t)14 * i + 7 + dd], q1 = xT[(size_t)14 * i + dd], v1 = xT[(size_t)14 * i + 7 + dd];
+    const double vl = oc.vl[dd], al = oc.al[dd], jl = oc.jl[dd];
+    double Tmin = 0, vco = 0;
+    bool bad = false;
+    if (act) {
+        bad = !(vl > 0 && al > 0 && jl > 0) || fabs(v0) > vl * (1 + 1e-12) || fabs(v1) > vl * (1 + 1e-12);
+        if (!bad) bad = !otg::min_time(q1 - q0, v0, v1, vl, al, jl, &Tmin, &vco);
+    }
+    bool fallback = (__ballot_sync(gmask, bad) & gmask) != 0;
+    double T = act && !bad ? Tmin : 0.0, vc = vco;
+    for (int o = 1; o < 8; o <<= 1) T = fmax(T, __shfl_xor_sync(gmask, T, o));
+    if (!fallback) {
+        bool all = false, need = false;
+        double lo = 0, hi = 0;
+        for (int round = 0; round < MPCB_OTG_ROUNDS && !all; round++) {
+            bool good = true;
+            double tn = T;
+            need = act && Tmin < T * (1 - 1e-15);
+            if (need) good = otg::sync_scan(q1 - q0, v0, v1, vl, al, jl, T, vco, &lo, &hi, &tn);
+            all = (__ballot_sync(gmask, !good) & gmask) == 0;
+            if (all) break;
+            for (int o = 1; o < 8; o <<= 1) tn = fmax(tn, __shfl_xor_sync(gmask, tn, o));
+            if (!(tn < INFINITY)) break;              // some joint has no profile that lasts T or longer
+            T = tn;                                   // the end of the blocked interval
+        }
+        fallback = !all || !(T > 0 && T <= oc.p_ub);
+        if (!fallback && need) vc = otg::sync_bisect(q1 - q0, v0, v1, al, jl, T, lo, hi);
+    }
+    const int N = oc.N;
+    if (!fallback) {
+        if (act) {
+            double t[7], j[7];
+            const otg::Eval e = otg::eval_vc(q1 - q0, v0, v1, vc, al, jl);
+            otg::dof_phases(v0, v1, vc, e.tc, al, jl, t, j);
+            for (int k = 0; k < N; k++) {
+                double q, v, a;
+                otg::dof_at_time(t, j, q0, v0, oc.tn[k] * T, &q, &v, &a);
+                gx[((size_t)i * N + k) * 14 + d] = q; gx[((size_t)i * N + k) * 14 + 7 + d] = v; gu[((size_t)i * N + k) * 7 + d] = a;
+            }
+        }
+    } else {
+        T = 0.05;
+        for (;;) {
+            const bool ok = !act || otg::hermite_ok(q1 - q0, v0, v1, T, vl, al);
+            const bool allok = (__ballot_sync(gmask, !ok) & gmask) == 0;
+            if (allok || T >= oc.p_ub) break;
+            T *= 1.05;
+            if (T > oc.p_ub) T = oc.p_ub;
+        }
+        if (act)
+            for (int k = 0; k < N; k++) {
+                double q, v, a;
+                otg::hermite_eval(q0, v0, q1, v1, T, oc.tn[k], &q, &v, &a);
+                gx[((size_t)i * N + k) * 14 + d] = q; gx[((size_t)i * N + k) * 14 + 7 + d] = v; gu[((size_t)i * N + k) * 7 + d] = a;
+            }
+    }
+    if (d == 0) gT[i] = T;
+}
+
 // ---- FP64 FMA peak ---------------------------------------------------------------------------------------------------
 __global__ void fp64_peak_kernel(double* out, int iters) {
     double a0 = threadIdx.x * 1e-3, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
@@ -273,6 +346,11 @@ cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double*
     cudaError_t e = cudaFuncSetAttribute(sample_kernel<SH36>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     sample_kernel<SH36><<<grid, SAMPLE_NT, smem, stream>>>(kc, sx, su, sT, target, npts, traj, acc, n);
+    return cudaGetLastError();
+}
+cudaError_t launch_otg_guess(const OtgConst& oc, int n, const double* x0, const double* xT, double* gx, double* gu, double* gT, cudaStream_t stream) {
+    const long long threads = 8ll * n;
+    otg_guess_kernel<<<(unsigned)((threads + OTG_NT - 1) / OTG_NT), OTG_NT, 0, stream>>>(oc, n, x0, xT, gx, gu, gT);
     return cudaGetLastError();
 }
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream) {

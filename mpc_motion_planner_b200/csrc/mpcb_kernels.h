@@ -14,6 +14,13 @@ struct KernelConst {
     double limtab[40];      // fill_limtab()
     double jmax[7];         // for the jerk flag of the accounting kernel
 };
+// Constants of the warm-start kernel (otg_guess_kernel): margins x limits per joint, the bound on T, the node times
+struct OtgConst {
+    double vl[7], al[7], jl[7];
+    double p_ub;
+    double tn[64];
+    int N;
+};
 // Device pointers of one batch (problem-major arrays, layouts in mpcb.h).
 struct BatchPtrs {
     const double *x0, *xT, *gx, *gu, *gT, *glam;
@@ -34,6 +41,8 @@ cudaError_t launch_node_val(const KernelConst& kc, int n, double* workspace, cud
 cudaError_t launch_admm(const KernelConst& kc, int n, int grid, int* counter, double* workspace, long long* prof, cudaStream_t stream);
 cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double* su, const double* sT, const double* target, int npts,
                           double* traj, mpcb_account* acc, int n, int grid, cudaStream_t stream);
+// warm start: jerk-limited synchronised profiles sampled at the node times (8 lanes per problem, one joint per lane)
+cudaError_t launch_otg_guess(const OtgConst& oc, int n, const double* x0, const double* xT, double* gx, double* gu, double* gT, cudaStream_t stream);
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream);
 
 }  // namespace mpcb

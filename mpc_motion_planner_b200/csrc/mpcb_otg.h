@@ -11,18 +11,21 @@
 //   step 1 (per joint): minimum duration = best of { cruise at +-v_max,  no cruise with the peak velocity vc that makes the
 //           two pulses cover the distance exactly }
 //   step 2: T = max over joints; every other joint lowers |vc| until its duration is T (the form the embedded
-//           trajectory shows for all six non-limiting joints); if a joint cannot meet T (a blocked interval), T grows.
-// Host code only (plain C++), no GPU work.
+//           trajectory shows for all six non-limiting joints); if a joint cannot meet T (a blocked interval), T moves to
+//           the end of that interval and all joints are synchronised again.
+// The per-joint routines compile for host and device: mpcb_guess_batch (host) and otg_guess_kernel (csrc/mpcb_kernels.cu, one
+// joint per lane) share them.
 #pragma once
 #include <math.h>
 #include "mpcb.h"
+#include "mpcb_common.h"
 
 namespace mpcb {
 namespace otg {
 
 struct Pulse { double tj, th, sgn; };      // jerk time, hold time, sign of the acceleration
 
-inline Pulse pulse(double va, double vb, double amax, double jmax) {
+MPCB_HD Pulse pulse(double va, double vb, double amax, double jmax) {
     Pulse p;
     const double dv = fabs(vb - va);
     p.sgn = vb >= va ? 1.0 : -1.0;
@@ -30,11 +33,11 @@ inline Pulse pulse(double va, double vb, double amax, double jmax) {
     else { p.tj = sqrt(dv / jmax); p.th = 0.0; }
     return p;
 }
-inline double ptime(const Pulse& p) { return 2.0 * p.tj + p.th; }
+MPCB_HD double ptime(const Pulse& p) { return 2.0 * p.tj + p.th; }
 
 // duration of the profile with cruise velocity vc, or -1 when the distance cannot be met with a cruise time >= 0
 struct Eval { double T, tc, dist; bool ok; };
-inline Eval eval_vc(double dp, double v0, double vT, double vc, double amax, double jmax) {
+MPCB_HD Eval eval_vc(double dp, double v0, double vT, double vc, double amax, double jmax) {
     const Pulse A = pulse(v0, vc, amax, jmax), B = pulse(vc, vT, amax, jmax);
     const double tA = ptime(A), tB = ptime(B);
     Eval e;
@@ -47,10 +50,10 @@ inline Eval eval_vc(double dp, double v0, double vT, double vc, double amax, dou
     return e;
 }
 
-constexpr int GRID = 512;
+#define MPCB_OTG_GRID 512
 
 // step 1: minimum duration and its cruise velocity
-inline bool min_time(double dp, double v0, double vT, double vmax, double amax, double jmax, double* Tmin, double* vcbest) {
+MPCB_HD bool min_time(double dp, double v0, double vT, double vmax, double amax, double jmax, double* Tmin, double* vcbest) {
     double best = INFINITY, bvc = 0;
     for (int s = -1; s <= 1; s += 2) {
         const Eval e = eval_vc(dp, v0, vT, s * vmax, amax, jmax);
@@ -58,8 +61,8 @@ inline bool min_time(double dp, double v0, double vT, double vmax, double amax, 
     }
     // no-cruise profiles: roots of h(vc) = dist(vc) - dp
     double vprev = -vmax, hprev = eval_vc(dp, v0, vT, vprev, amax, jmax).dist - dp;
-    for (int i = 1; i <= GRID; i++) {
-        const double vcur = -vmax + 2.0 * vmax * i / GRID, hcur = eval_vc(dp, v0, vT, vcur, amax, jmax).dist - dp;
+    for (int i = 1; i <= MPCB_OTG_GRID; i++) {
+        const double vcur = -vmax + 2.0 * vmax * i / MPCB_OTG_GRID, hcur = eval_vc(dp, v0, vT, vcur, amax, jmax).dist - dp;
         if (hprev == 0.0 || (hprev < 0) != (hcur < 0)) {
             double lo = vprev, hi = vcur, hlo = hprev;
             for (int it = 0; it < 80; it++) {
@@ -77,41 +80,105 @@ inline bool min_time(double dp, double v0, double vT, double vmax, double amax, 
     return best < INFINITY;
 }
 
-// step 2: cruise velocity whose profile lasts exactly T (searched from the time-optimal vc towards 0)
-inline bool sync_vc(double dp, double v0, double vT, double vmax, double amax, double jmax, double T, double vcopt, double* vc) {
-    const double dir = vcopt >= 0 ? 1.0 : -1.0;
-    double vprev = vcopt;
+// step 2: cruise velocity whose profile lasts exactly T.  The candidates are scanned from the time-optimal vc towards 0 and on
+// to the other velocity limit over a fixed grid (MPCB_OTG_SYNC cells over [-vmax, vmax]; vc = 0 is a grid point).  Between two
+// neighbouring candidates of the same sign the duration is continuous, so the pair reaches every duration between theirs; next
+// to vc = 0 the cruise time grows without bound when the remaining distance has the sign of vc.
+//   returns true  and the bracket [*lo, *hi] (duration(*lo) < T iff *lolt) when some pair reaches T;
+//   returns false and *Tnext = the smallest reachable duration above T (INFINITY if none: T lies past every profile of this
+//   joint), which is where a blocked interval of this joint ends.
+#define MPCB_OTG_SYNC 1024
+MPCB_HD double sync_grid(double vmax, int k) { return k == MPCB_OTG_SYNC / 2 ? 0.0 : -vmax + 2.0 * vmax * k / MPCB_OTG_SYNC; }
+MPCB_HD bool sync_scan(double dp, double v0, double vT, double vmax, double amax, double jmax, double T, double vcopt, double* lo, double* hi,
+                       double* Tnext) {
+    const int dir = vcopt >= 0 ? 1 : -1;
+    // first grid point strictly past vcopt in the scan direction
+    int k = (int)floor((vcopt + vmax) / (2.0 * vmax) * MPCB_OTG_SYNC);
+    k = k < 0 ? 0 : (k > MPCB_OTG_SYNC ? MPCB_OTG_SYNC : k);
+    if (dir > 0) { while (k >= 0 && sync_grid(vmax, k) >= vcopt) k--; }
+    else { k++; while (k <= MPCB_OTG_SYNC && sync_grid(vmax, k) <= vcopt) k++; }
+    const double rest0 = dp - eval_vc(dp, v0, vT, 0.0, amax, jmax).dist;     // distance left to a cruise at vc -> 0
+    double vprev = vcopt, tnext = INFINITY;
     Eval eprev = eval_vc(dp, v0, vT, vprev, amax, jmax);
-    if (eprev.ok && fabs(eprev.T - T) <= 1e-13 * fmax(1.0, T)) { *vc = vprev; return true; }
-    // scan |vc| downwards through 0 to the other limit
-    for (int i = 1; i <= 2 * GRID; i++) {
-        const double vcur = vcopt - dir * (fabs(vcopt) + vmax) * i / (2 * GRID);
-        if (fabs(vcur) > vmax) break;
+    for (; k >= 0 && k <= MPCB_OTG_SYNC; k -= dir) {
+        const double vcur = sync_grid(vmax, k);
         const Eval ecur = eval_vc(dp, v0, vT, vcur, amax, jmax);
-        if (eprev.ok && ecur.ok && (eprev.T < T) != (ecur.T < T) && (vprev > 0) == (vcur > 0)) {
-            double lo = vprev, hi = vcur;
-            const bool lolt = eprev.T < T;
-            for (int it = 0; it < 80; it++) {
-                const double mid = 0.5 * (lo + hi);
-                const Eval em = eval_vc(dp, v0, vT, mid, amax, jmax);
-                if (em.ok && (em.T < T) == lolt) lo = mid; else hi = mid;
-            }
-            *vc = 0.5 * (lo + hi);
-            return true;
+        // the pair reaches the durations (plo, phi] (empty when phi < plo); blo is the end with the shorter duration
+        double plo = 0, phi = -1, blo = vprev, bhi = vcur;
+        if (eprev.ok && ecur.ok && ((vprev > 0) == (vcur > 0) || vprev == 0.0 || vcur == 0.0)) {
+            plo = fmin(eprev.T, ecur.T); phi = fmax(eprev.T, ecur.T);
+            if (ecur.T < eprev.T) { blo = vcur; bhi = vprev; }
+        } else if (vcur == 0.0 && eprev.ok && rest0 * vprev > 0) { plo = eprev.T; phi = INFINITY; }
+        else if (vprev == 0.0 && ecur.ok && rest0 * vcur > 0) { plo = ecur.T; phi = INFINITY; blo = vcur; bhi = vprev; }
+        if (phi >= plo) {
+            if (T > plo && T <= phi) { *lo = blo; *hi = bhi; *Tnext = T; return true; }
+            if (plo >= T) tnext = fmin(tnext, plo * (1.0 + 1e-12) + 1e-300);
         }
         vprev = vcur; eprev = ecur;
     }
+    *Tnext = tnext;
     return false;
 }
+// bisection inside the bracket of sync_scan
+MPCB_HD double sync_bisect(double dp, double v0, double vT, double amax, double jmax, double T, double lo, double hi) {
+    for (int it = 0; it < 80; it++) {
+        const double mid = 0.5 * (lo + hi);
+        const Eval em = eval_vc(dp, v0, vT, mid, amax, jmax);
+        if (em.ok && em.T < T) lo = mid; else hi = mid;
+    }
+    return 0.5 * (lo + hi);
+}
+#define MPCB_OTG_ROUNDS 16       // blocked intervals skipped before the input is given up
 
-inline void fill_dof(mpcb_otg_traj* tr, int d, double q0, double v0, double vT, double vc, double tc, double amax, double jmax) {
+// the 7 constant-jerk phases of one joint: durations t[7] and jerks j[7]
+MPCB_HD void dof_phases(double v0, double vT, double vc, double tc, double amax, double jmax, double* t, double* j) {
     const Pulse A = pulse(v0, vc, amax, jmax), B = pulse(vc, vT, amax, jmax);
-    double* t = tr->t[d];
-    double* j = tr->j[d];
     t[0] = A.tj; j[0] = A.sgn * jmax; t[1] = A.th; j[1] = 0; t[2] = A.tj; j[2] = -A.sgn * jmax;
     t[3] = tc; j[3] = 0;
     t[4] = B.tj; j[4] = B.sgn * jmax; t[5] = B.th; j[5] = 0; t[6] = B.tj; j[6] = -B.sgn * jmax;
+}
+// state of one joint at time `time` (clamped below at 0; constant velocity past the end, as Ruckig's at_time)
+MPCB_HD void dof_at_time(const double* t, const double* j, double q0, double v0, double time, double* q, double* v, double* a) {
+    double p = q0, vel = v0, acc = 0, left = time < 0 ? 0 : time;
+    for (int ph = 0; ph < 7; ph++) {
+        const double dt = left < t[ph] ? left : t[ph], jj = j[ph];
+        p += dt * (vel + dt * (0.5 * acc + dt * jj / 6.0));
+        vel += dt * (acc + 0.5 * dt * jj);
+        acc += dt * jj;
+        left -= dt;
+        if (left <= 0) break;
+    }
+    if (left > 0) p += vel * left;
+    *q = p; *v = vel; *a = acc;
+}
+inline void fill_dof(mpcb_otg_traj* tr, int d, double q0, double v0, double vT, double vc, double tc, double amax, double jmax) {
+    dof_phases(v0, vT, vc, tc, amax, jmax, tr->t[d], tr->j[d]);
     tr->q0[d] = q0; tr->v0[d] = v0; tr->vc[d] = vc;
+}
+
+// ---- fallback for inputs the generator rejects: time-scaled cubic Hermite profile q(s), s = t / T ---------------------------
+// one joint respects |v| <= vl over [0, T] and |a| <= al (the acceleration is linear in s: extrema at the ends; the velocity
+// is quadratic: extrema at the ends or at the vertex)
+MPCB_HD bool hermite_ok(double dq, double v0, double v1, double T, double vl, double al) {
+    const double a0 = (6 * dq / T - 4 * v0 - 2 * v1) / T, a1 = (-6 * dq / T + 2 * v0 + 4 * v1) / T;
+    if (fabs(a0) > al || fabs(a1) > al) return false;
+    if (a1 != a0) {
+        const double sv = -a0 / (a1 - a0);
+        if (sv > 0 && sv < 1) {
+            const double vv = v0 + a0 * T * sv + 0.5 * (a1 - a0) * T * sv * sv;
+            if (fabs(vv) > vl) return false;
+        }
+    }
+    return true;
+}
+MPCB_HD void hermite_eval(double q0, double v0, double q1, double v1, double T, double sg, double* q, double* v, double* a) {
+    const double h00 = 2 * sg * sg * sg - 3 * sg * sg + 1, h10 = sg * sg * sg - 2 * sg * sg + sg, h01 = -2 * sg * sg * sg + 3 * sg * sg,
+                 h11 = sg * sg * sg - sg * sg;
+    const double d00 = 6 * sg * sg - 6 * sg, d10 = 3 * sg * sg - 4 * sg + 1, d01 = -6 * sg * sg + 6 * sg, d11 = 3 * sg * sg - 2 * sg;
+    const double e00 = 12 * sg - 6, e10 = 6 * sg - 4, e01 = -12 * sg + 6, e11 = 6 * sg - 2;
+    *q = h00 * q0 + h10 * T * v0 + h01 * q1 + h11 * T * v1;
+    *v = (d00 * q0 + d10 * T * v0 + d01 * q1 + d11 * T * v1) / T;
+    *a = (e00 * q0 + e10 * T * v0 + e01 * q1 + e11 * T * v1) / (T * T);
 }
 
 // 0 = ok, 1 = ok after growing T past a blocked interval, < 0 = no profile (input outside the limits)
@@ -126,37 +193,34 @@ inline int calculate(const mpcb_limits* lim, const double* x0, const double* xT,
         if (Tmin[d] > T) T = Tmin[d];
     }
     int status = 0;
-    for (int attempt = 0; attempt < 400; attempt++) {
-        bool all = true;
-        for (int d = 0; d < 7 && all; d++) {
-            double vc = vco[d];
-            if (Tmin[d] < T * (1 - 1e-15)) all = sync_vc(xT[d] - x0[d], x0[7 + d], xT[7 + d], vl[d], al[d], jl[d], T, vco[d], &vc);
-            if (all) {
-                const Eval e = eval_vc(xT[d] - x0[d], x0[7 + d], xT[7 + d], vc, al[d], jl[d]);
-                fill_dof(tr, d, x0[d], x0[7 + d], xT[7 + d], vc, e.tc, al[d], jl[d]);
-            }
+    double lo[7], hi[7];
+    bool need[7], all = false;
+    for (int round = 0; round < MPCB_OTG_ROUNDS && !all; round++) {
+        all = true;
+        double Tn = T;
+        for (int d = 0; d < 7; d++) {
+            need[d] = Tmin[d] < T * (1 - 1e-15);
+            if (!need[d]) continue;
+            double tn;
+            if (!sync_scan(xT[d] - x0[d], x0[7 + d], xT[7 + d], vl[d], al[d], jl[d], T, vco[d], &lo[d], &hi[d], &tn)) { all = false; Tn = fmax(Tn, tn); }
         }
-        if (all) { tr->T = T; tr->status = status; return status; }
-        T *= 1.005; status = 1;
+        if (all) break;
+        if (!(Tn < INFINITY)) return -4;          // some joint has no profile that lasts T or longer
+        T = Tn; status = 1;                        // the end of the blocked interval
     }
-    return -4;
+    if (!all) return -4;
+    for (int d = 0; d < 7; d++) {
+        const double dp = xT[d] - x0[d];
+        const double vc = need[d] ? sync_bisect(dp, x0[7 + d], xT[7 + d], al[d], jl[d], T, lo[d], hi[d]) : vco[d];
+        const Eval e = eval_vc(dp, x0[7 + d], xT[7 + d], vc, al[d], jl[d]);
+        fill_dof(tr, d, x0[d], x0[7 + d], xT[7 + d], vc, e.tc, al[d], jl[d]);
+    }
+    tr->T = T; tr->status = status;
+    return status;
 }
 
 inline void at_time(const mpcb_otg_traj* tr, double t, double* q, double* v, double* a) {
-    if (t < 0) t = 0;
-    for (int d = 0; d < 7; d++) {
-        double p = tr->q0[d], vel = tr->v0[d], acc = 0, left = t;
-        for (int ph = 0; ph < 7; ph++) {
-            const double dt = left < tr->t[d][ph] ? left : tr->t[d][ph], j = tr->j[d][ph];
-            p += dt * (vel + dt * (0.5 * acc + dt * j / 6.0));
-            vel += dt * (acc + 0.5 * dt * j);
-            acc += dt * j;
-            left -= dt;
-            if (left <= 0) break;
-        }
-        if (left > 0) { p += vel * left; }       // past the end: constant velocity, as Ruckig's at_time does
-        q[d] = p; v[d] = vel; a[d] = acc;
-    }
+    for (int d = 0; d < 7; d++) dof_at_time(tr->t[d], tr->j[d], tr->q0[d], tr->v0[d], t, q + d, v + d, a + d);
 }
 
 }  // namespace otg

@@ -293,37 +293,17 @@ int mpcb_guess_batch(const mpcb_settings* s, const mpcb_limits* lim, int n, cons
         double T = 0.05;
         for (;;) {
             bool ok = true;
-            for (int j = 0; j < 7 && ok; j++) {
-                const double dq = q1[j] - q0[j], vl = lim->margins[1] * lim->vmax[j], al = lim->margins[2] * lim->amax[j];
-                const double a0 = (6 * dq / T - 4 * v0[j] - 2 * v1[j]) / T, a1 = (-6 * dq / T + 2 * v0[j] + 4 * v1[j]) / T;
-                if (fabs(a0) > al || fabs(a1) > al) { ok = false; break; }
-                // v(s) = v0 + a0 T s + (a1 - a0) T s^2 / 2 ; vertex at s* = -a0 / (a1 - a0)
-                if (a1 != a0) {
-                    const double sv = -a0 / (a1 - a0);
-                    if (sv > 0 && sv < 1) {
-                        const double vv = v0[j] + a0 * T * sv + 0.5 * (a1 - a0) * T * sv * sv;
-                        if (fabs(vv) > vl) ok = false;
-                    }
-                }
-            }
+            for (int j = 0; j < 7 && ok; j++)
+                ok = otg::hermite_ok(q1[j] - q0[j], v0[j], v1[j], T, lim->margins[1] * lim->vmax[j], lim->margins[2] * lim->amax[j]);
             if (ok || T >= lim->p_ub) break;
             T *= 1.05;
             if (T > lim->p_ub) T = lim->p_ub;
         }
         gT[i] = T;
         for (int k = 0; k < N; k++) {
-            const double sg = tn[k];
-            const double h00 = 2 * sg * sg * sg - 3 * sg * sg + 1, h10 = sg * sg * sg - 2 * sg * sg + sg, h01 = -2 * sg * sg * sg + 3 * sg * sg,
-                         h11 = sg * sg * sg - sg * sg;
-            const double d00 = 6 * sg * sg - 6 * sg, d10 = 3 * sg * sg - 4 * sg + 1, d01 = -6 * sg * sg + 6 * sg, d11 = 3 * sg * sg - 2 * sg;
-            const double e00 = 12 * sg - 6, e10 = 6 * sg - 4, e01 = -12 * sg + 6, e11 = 6 * sg - 2;
             double* xk = gx + ((size_t)i * N + k) * 14;
             double* uk = gu + ((size_t)i * N + k) * 7;
-            for (int j = 0; j < 7; j++) {
-                xk[j] = h00 * q0[j] + h10 * T * v0[j] + h01 * q1[j] + h11 * T * v1[j];
-                xk[7 + j] = (d00 * q0[j] + d10 * T * v0[j] + d01 * q1[j] + d11 * T * v1[j]) / T;
-                uk[j] = (e00 * q0[j] + e10 * T * v0[j] + e01 * q1[j] + e11 * T * v1[j]) / (T * T);
-            }
+            for (int j = 0; j < 7; j++) otg::hermite_eval(q0[j], v0[j], q1[j], v1[j], T, tn[k], xk + j, xk + 7 + j, uk + j);
         }
     }
     return MPCB_OK;

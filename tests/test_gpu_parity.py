@@ -75,6 +75,25 @@ def test_embedded_reference_problem(oracle, solver):
     assert abs(sT[0] - 1.55469) < 0.08
 
 
+@pytest.mark.parametrize("kind,seed,margins", [(0, 1, BENCH_MARGINS), (1, 0, OFFLINE_MARGINS)])
+def test_device_warm_start_matches_host(solver, kind, seed, margins):
+    """otg_guess_kernel (8 lanes per problem, one joint per lane) against the host generator it shares its per-joint
+    routines with: same duration and node samples up to multiply-add contraction, for accepted inputs and for the
+    cubic-Hermite fallback of rejected ones."""
+    n = 300
+    s, lim, x0, xT, gx, gu, gT = _problems(kind, seed, n, margins)
+    x0 = x0.copy(); xT = xT.copy()
+    xT[::17, 7] = 1.01 * margins[1] * lim.vmax[0]          # a target velocity outside the margin: the generator rejects it
+    gx, gu, gT = M.guess_batch(s, lim, x0, xT)
+    solver.set_limits(lim)
+    dx, du, dT = solver.guess(x0, xT)
+    assert np.abs(dT - gT).max() <= 1e-12 * np.abs(gT).max()
+    assert np.abs(dx - gx).max() < 1e-10 and np.abs(du - gu).max() < 1e-8      # a(t) has slope j ~ 1e3: 1e-12 in t -> 1e-9 in a
+    # the device guess drives the solver to the same result (tolerances of the parity contract)
+    a = solver.solve(x0[:8], xT[:8], gx[:8], gu[:8], gT[:8]); b = solver.solve(x0[:8], xT[:8], dx[:8], du[:8], dT[:8])
+    assert np.abs(a[2] - b[2]).max() <= 1e-6 * np.abs(a[2]).max() and np.abs(a[0] - b[0]).max() < 1e-5
+
+
 def test_receding_horizon_resolve(oracle, solver):
     """BASELINE config 5: re-solve 1 ms later, warm-started from the previous solution INCLUDING its multipliers
     (motionPlanner.cpp:199-207 re-seed + polympc's dual carry-over) -- the guess_lam / sol_lam arguments."""

@@ -272,6 +272,15 @@ def run_ours(args):
         a.record(); sv.guess_device(B, dx0.data_ptr(), dxT.data_ptr(), dgx.data_ptr(), dgu.data_ptr(), dgT.data_ptr(), stream); b.record()
         torch.cuda.synchronize(); wg.append(a.elapsed_time(b))
     line["stats"]["warm_start_kernel_ms"] = float(sorted(wg)[len(wg) // 2])
+    # the problem generator on the device (gen_problems_kernel: this rank's shard of the seed-1 batch), into scratch buffers
+    tx0 = torch.empty_like(dx0); txT = torch.empty_like(dxT)
+    wg = []
+    for _ in range(4):
+        a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+        a.record(); sv.generate_device(0, 1, B, tx0.data_ptr(), txT.data_ptr(), first=lo, stream=stream); b.record()
+        torch.cuda.synchronize(); wg.append(a.elapsed_time(b))
+    line["stats"]["problem_generator_kernel_ms"] = float(sorted(wg)[len(wg) // 2])
+    line["stats"]["problem_generator_max_abs_diff_vs_host"] = float(max((tx0.cpu() - torch.from_numpy(x0)).abs().max(), (txT.cpu() - torch.from_numpy(xT)).abs().max()))
     # BASELINE config 5 (receding horizon, latency bound): batch of 8 re-solved 40 times, each time warm-started from the
     # previous solution and its multipliers (guess_lam = previous sol_lam), device-resident
     nd = sv.ndual

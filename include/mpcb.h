@@ -189,6 +189,12 @@ int mpcb_guess_batch(const mpcb_settings* s, const mpcb_limits* lim, int n, cons
 int mpcb_guess_batch_gpu(mpcb_handle* h, int n, const double* x0, const double* xT, double* guess_x, double* guess_u, double* guess_T,
                          int mem, void* cuda_stream);
 
+/* mpcb_generate_problems on the device of handle `h` with its current limits (gen_problems_kernel, one problem per thread): problem i of
+ * the call draws from stream (seed, first + i), so a rank generates its shard [first, first + n) of a batch in place.  Same routines as
+ * the host version; results agree to rounding (device sin/cos and contracted multiply-adds). */
+int mpcb_generate_problems_gpu(mpcb_handle* h, int kind, unsigned long long seed, unsigned long long first, int n, double* x0, double* xT,
+                               int mem, void* cuda_stream);
+
 /* Single-state host helpers used by the C++ MotionPlanner mirror (include/motion_planner.hpp):
  *   mpcb_sample_random_state  MotionPlanner::sample_random_state (motionPlanner.cpp:102-114), counter-based RNG (seed, stream)
  *   mpcb_forward_velocities   PandaWrapper::forward_velocities (robot_utils/pandaWrapper.cpp:90-107): tool twist [lin; ang]

@@ -233,6 +233,20 @@ class Solver:
                                          C.c_void_p(stream) if stream else None)
         self._check(rc, "mpcb_guess_batch_gpu")
 
+    def generate(self, kind, seed, n, first=0):
+        """Problem generation on the device (mpcb_generate_problems_gpu): problems [first, first + n) of the batch of `seed`."""
+        x0 = np.zeros((n, 14)); xT = np.zeros((n, 14))
+        rc = self.L.mpcb_generate_problems_gpu(self.h, C.c_int(kind), C.c_ulonglong(seed), C.c_ulonglong(first), C.c_int(n), _p(x0), _p(xT),
+                                               C.c_int(MEM_HOST), None)
+        self._check(rc, "mpcb_generate_problems_gpu")
+        return x0, xT
+
+    def generate_device(self, kind, seed, n, x0, xT, first=0, stream=0):
+        """Device-pointer form (raw addresses); only enqueues the kernel."""
+        rc = self.L.mpcb_generate_problems_gpu(self.h, C.c_int(kind), C.c_ulonglong(seed), C.c_ulonglong(first), C.c_int(n), _p(x0), _p(xT),
+                                               C.c_int(MEM_DEVICE), C.c_void_p(stream) if stream else None)
+        self._check(rc, "mpcb_generate_problems_gpu")
+
     def sample(self, sx, su, sT, target=None, npts=200, want_traj=True, want_acc=True):
         sx = _d(np.atleast_2d(sx)); su = _d(np.atleast_2d(su)); sT = _d(np.atleast_1d(sT))
         n = sT.shape[0]

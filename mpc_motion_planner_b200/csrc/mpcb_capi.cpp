@@ -334,6 +334,31 @@ int mpcb_guess_batch_gpu(mpcb_handle* h, int n, const double* x0, const double* 
     return MPCB_OK;
 }
 
+int mpcb_generate_problems_gpu(mpcb_handle* h, int kind, unsigned long long seed, unsigned long long first, int n, double* x0, double* xT, int mem,
+                               void* stream_) {
+    if (!h) return MPCB_ERR_BAD_ARG;
+    if (n < 0 || (n > 0 && (!x0 || !xT)) || (kind != 0 && kind != 1)) { h->err = "bad argument"; return MPCB_ERR_BAD_ARG; }
+    if (mem != MPCB_MEM_HOST && mem != MPCB_MEM_DEVICE) { h->err = "mem must be MPCB_MEM_HOST or MPCB_MEM_DEVICE"; return MPCB_ERR_BAD_ARG; }
+    if (n == 0) return MPCB_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CK(cudaSetDevice(h->device));
+    const size_t b14 = sizeof(double) * 14 * n;
+    double *da = x0, *db = xT;
+    if (mem == MPCB_MEM_HOST) {
+        int rc = ensure_stage(h, 2 * al(b14));
+        if (rc) return rc;
+        da = (double*)h->d_stage; db = (double*)((char*)h->d_stage + al(b14));
+    }
+    CK(launch_gen_problems(h->lim, kind, seed, first, n, da, db, stream));
+    h->launches += 1;
+    if (mem == MPCB_MEM_HOST) {
+        CK(cudaMemcpyAsync(x0, da, b14, cudaMemcpyDeviceToHost, stream));
+        CK(cudaMemcpyAsync(xT, db, b14, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+    }
+    return MPCB_OK;
+}
+
 double mpcb_last_solve_ms(mpcb_handle* h) {
     if (!h || !h->timed) return -1.0;
     cudaSetDevice(h->device);

@@ -11,6 +11,7 @@
 #include <stdint.h>
 
 #include "mpcb_kernels.h"
+#include "mpcb_gen.h"
 #include "mpcb_otg.h"
 #include "mpcb_sqp.h"
 
@@ -298,6 +299,18 @@ otg_guess_kernel(const __grid_constant__ OtgConst oc, const int n, const double*
     if (d == 0) gT[i] = T;
 }
 
+// ---- problem generator: one problem per thread (the routines of mpcb_gen.h, shared with mpcb_generate_problems) -----------------
+constexpr int GEN_NT = 32;       // small CTAs: the rejection loop and the 6x6 solve are long serial chains, spread them over the SMs
+__global__ void __launch_bounds__(GEN_NT)
+gen_problems_kernel(const __grid_constant__ mpcb_limits lim, const int kind, const unsigned long long seed, const unsigned long long first,
+                    const int n, double* __restrict__ x0, double* __restrict__ xT) {
+    const int i = blockIdx.x * GEN_NT + threadIdx.x;
+    if (i >= n) return;
+    double a[14], b[14];
+    gen::generate_one(&lim, kind, seed, first + (unsigned long long)i, a, b);
+    for (int k = 0; k < 14; k++) { x0[(size_t)14 * i + k] = a[k]; xT[(size_t)14 * i + k] = b[k]; }
+}
+
 // ---- FP64 FMA peak ---------------------------------------------------------------------------------------------------
 __global__ void fp64_peak_kernel(double* out, int iters) {
     double a0 = threadIdx.x * 1e-3, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
@@ -351,6 +364,11 @@ cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double*
 cudaError_t launch_otg_guess(const OtgConst& oc, int n, const double* x0, const double* xT, double* gx, double* gu, double* gT, cudaStream_t stream) {
     const long long threads = 8ll * n;
     otg_guess_kernel<<<(unsigned)((threads + OTG_NT - 1) / OTG_NT), OTG_NT, 0, stream>>>(oc, n, x0, xT, gx, gu, gT);
+    return cudaGetLastError();
+}
+cudaError_t launch_gen_problems(const mpcb_limits& lim, int kind, unsigned long long seed, unsigned long long first, int n, double* x0, double* xT,
+                                cudaStream_t stream) {
+    gen_problems_kernel<<<(unsigned)((n + GEN_NT - 1) / GEN_NT), GEN_NT, 0, stream>>>(lim, kind, seed, first, n, x0, xT);
     return cudaGetLastError();
 }
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream) {

@@ -43,6 +43,9 @@ cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double*
                           double* traj, mpcb_account* acc, int n, int grid, cudaStream_t stream);
 // warm start: jerk-limited synchronised profiles sampled at the node times (8 lanes per problem, one joint per lane)
 cudaError_t launch_otg_guess(const OtgConst& oc, int n, const double* x0, const double* xT, double* gx, double* gu, double* gT, cudaStream_t stream);
+// problem generator: problem i of the launch draws from stream (seed, first + i)
+cudaError_t launch_gen_problems(const mpcb_limits& lim, int kind, unsigned long long seed, unsigned long long first, int n, double* x0, double* xT,
+                                cudaStream_t stream);
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream);
 
 }  // namespace mpcb

@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include "mpcb.h"
+#include "mpcb_gen.h"
 #include "mpcb_host_util.h"
 #include "mpcb_otg.h"
 #include "mpcb_rbd.h"
@@ -21,85 +22,7 @@ namespace {
 
 using namespace mpcb;
 
-// counter-based RNG: splitmix64 of (seed, stream, counter) -> U(-1,1)   (replaces Eigen::Random / std::rand, Q13)
-struct Rng {
-    uint64_t state;
-    Rng(uint64_t seed, uint64_t stream) : state(seed * 0x9E3779B97F4A7C15ull + stream * 0xD1B54A32D192ED03ull + 0x632BE59BD9B4E019ull) {}
-    uint64_t next() {
-        uint64_t z = (state += 0x9E3779B97F4A7C15ull);
-        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-        return z ^ (z >> 31);
-    }
-    double sym() { return 2.0 * ((next() >> 11) * (1.0 / 9007199254740992.0)) - 1.0; }
-};
-
-const double MAX_LINEAR_VELOCITY = 1.7, MAX_ANGULAR_VELOCITY = 2.5;   // pandaWrapper.hpp:37-38
-
-// world-aligned tool Jacobian (6x7)
-void tool_jacobian(const double* q, double* J) {
-    double oR[7][9], op[7][3];
-    rbd::fk_world(q, oR, op);
-    rbd::frame_jacobian(oR, op, PANDA(PANDA_TOOL_OFFSET), J, nullptr);
-}
-void forward_velocities(const double* q, const double* qd, double* tv) {    // pandaWrapper.cpp:90-107
-    double J[42];
-    tool_jacobian(q, J);
-    for (int r = 0; r < 6; r++) { double s = 0; for (int j = 0; j < 7; j++) s += J[r * 7 + j] * qd[j]; tv[r] = s; }
-}
-// J^T (J J^T + 1e-5 I)^-1 v   with an LDL^T solve of the 6x6 system                  // pandaWrapper.cpp:60-88
-void inverse_velocities(const double* q, const double* task, double* qd) {
-    double J[42], A[36], L[36], D[6], y[6];
-    tool_jacobian(q, J);
-    for (int r = 0; r < 6; r++)
-        for (int c = 0; c < 6; c++) { double s = 0; for (int j = 0; j < 7; j++) s += J[r * 7 + j] * J[c * 7 + j]; A[r * 6 + c] = s + (r == c ? 1e-5 : 0.0); }
-    memset(L, 0, sizeof L);
-    for (int j = 0; j < 6; j++) {
-        double d = A[j * 6 + j];
-        for (int k = 0; k < j; k++) d -= L[j * 6 + k] * L[j * 6 + k] * D[k];
-        D[j] = d; L[j * 6 + j] = 1;
-        for (int i = j + 1; i < 6; i++) {
-            double s = A[i * 6 + j];
-            for (int k = 0; k < j; k++) s -= L[i * 6 + k] * L[j * 6 + k] * D[k];
-            L[i * 6 + j] = s / d;
-        }
-    }
-    for (int i = 0; i < 6; i++) { double s = task[i]; for (int k = 0; k < i; k++) s -= L[i * 6 + k] * y[k]; y[i] = s; }
-    for (int i = 0; i < 6; i++) y[i] /= D[i];
-    for (int i = 5; i >= 0; i--) { double s = y[i]; for (int k = i + 1; k < 6; k++) s -= L[k * 6 + i] * y[k]; y[i] = s; }
-    for (int j = 0; j < 7; j++) { double s = 0; for (int r = 0; r < 6; r++) s += J[r * 7 + j] * y[r]; qd[j] = s; }
-}
-double norm3(const double* v) { return sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); }
-
-// sample_random_state (motionPlanner.cpp:102-114): rejection on the height of JOINT 7 (not the tool, Q12)
-void sample_random_state(const mpcb_limits* lim, Rng& rng, double* q, double* v) {
-    const double mp = lim->margins[0], mv = lim->margins[1];
-    const double zero[3] = {0, 0, 0};
-    double pos[3];
-    do {
-        for (int j = 0; j < 7; j++) {
-            const double range = lim->qmax[j] - lim->qmin[j];
-            const double safety = (1 - mp) * range / 2;
-            q[j] = 0.5 * (rng.sym() * (range - 2 * safety) + (lim->qmax[j] + lim->qmin[j]));
-        }
-        rbd::fk_point7(q, zero, pos);
-    } while (pos[2] < lim->min_height);
-    for (int j = 0; j < 7; j++) v[j] = mv * rng.sym() * lim->vmax[j];
-}
-// Cartesian scale-downs shared by both examples (benchmark.cpp:25-36, offline_trajectory.cpp:26-39)
-void scale_task_velocity(const double* q, double* v) {
-    double tv[6];
-    forward_velocities(q, v, tv);
-    if (norm3(tv) > MAX_LINEAR_VELOCITY) {
-        const double f = 0.9 * MAX_LINEAR_VELOCITY / norm3(tv);
-        for (int j = 0; j < 7; j++) v[j] *= f;
-        forward_velocities(q, v, tv);
-    }
-    if (norm3(tv + 3) > MAX_ANGULAR_VELOCITY) {
-        const double f = 0.9 * MAX_ANGULAR_VELOCITY / norm3(tv + 3);
-        for (int j = 0; j < 7; j++) v[j] *= f;
-    }
-}
+using namespace mpcb::gen;
 
 }  // namespace
 
@@ -107,31 +30,7 @@ extern "C" {
 
 int mpcb_generate_problems(const mpcb_limits* lim, int kind, unsigned long long seed, int n, double* x0, double* xT) {
     if (!lim || !x0 || !xT || n < 0 || (kind != 0 && kind != 1)) return MPCB_ERR_BAD_ARG;
-    for (int i = 0; i < n; i++) {
-        Rng rng(seed, (uint64_t)i);
-        double* a = x0 + 14 * (size_t)i;
-        double* b = xT + 14 * (size_t)i;
-        if (kind == 0) {
-            // start: mid-range pose at rest (MotionPlanner constructor, motionPlanner.cpp:5-8; never reset in benchmark.cpp)
-            for (int j = 0; j < 7; j++) { a[j] = (lim->qmax[j] + lim->qmin[j]) / 2; a[7 + j] = 0; }
-            sample_random_state(lim, rng, b, b + 7);
-            double task[6] = {rng.sym() * MAX_LINEAR_VELOCITY, rng.sym() * MAX_LINEAR_VELOCITY, rng.sym() * MAX_LINEAR_VELOCITY, 0, 0, 0};
-            inverse_velocities(b, task, b + 7);                                     // benchmark.cpp:20
-            scale_task_velocity(b, b + 7);                                          // benchmark.cpp:22-36
-            double worst = 0;                                                       // benchmark.cpp:38-42
-            bool any = false;
-            for (int j = 0; j < 7; j++) {
-                const double r = fabs(b[7 + j]) / (lim->margins[1] * lim->vmax[j]);
-                if (r > 1) any = true;
-                if (r > worst) worst = r;
-            }
-            if (any) for (int j = 0; j < 7; j++) b[7 + j] /= 1.1 * worst;
-        } else {
-            sample_random_state(lim, rng, a, a + 7);                                // offline_trajectory.cpp:18-19
-            sample_random_state(lim, rng, b, b + 7);                                // :22
-            scale_task_velocity(b, b + 7);                                          // :26-39
-        }
-    }
+    for (int i = 0; i < n; i++) generate_one(lim, kind, seed, (uint64_t)i, x0 + 14 * (size_t)i, xT + 14 * (size_t)i);
     return MPCB_OK;
 }
 

@@ -94,6 +94,22 @@ def test_device_warm_start_matches_host(solver, kind, seed, margins):
     assert np.abs(a[2] - b[2]).max() <= 1e-6 * np.abs(a[2]).max() and np.abs(a[0] - b[0]).max() < 1e-5
 
 
+@pytest.mark.parametrize("kind,seed,margins", [(0, 1, BENCH_MARGINS), (1, 0, OFFLINE_MARGINS)])
+def test_device_generator_matches_host(solver, kind, seed, margins):
+    """gen_problems_kernel (one problem per thread) against mpcb_generate_problems: the same counter-based streams and the same
+    routines, so the same problems up to device sin/cos rounding; a shard [first, first + n) equals the slice of the full batch."""
+    n = 2000
+    lim = M.default_limits(margins)
+    x0, xT = M.generate_problems(lim, kind, seed, n)
+    solver.set_limits(lim)
+    d0, dT = solver.generate(kind, seed, n)
+    # positions: affine in the uniform draws; velocities of kind 0 pass through (J J^T + 1e-5 I)^-1, which amplifies the
+    # sin/cos rounding differences near singular poses (2.9e-12 observed)
+    assert np.abs(d0 - x0).max() < 1e-13 and np.abs(dT[:, :7] - xT[:, :7]).max() < 1e-13 and np.abs(dT[:, 7:] - xT[:, 7:]).max() < 1e-9
+    p0, pT = solver.generate(kind, seed, 300, first=1500)
+    assert np.array_equal(p0, d0[1500:1800]) and np.array_equal(pT, dT[1500:1800])
+
+
 def test_receding_horizon_resolve(oracle, solver):
     """BASELINE config 5: re-solve 1 ms later, warm-started from the previous solution INCLUDING its multipliers
     (motionPlanner.cpp:199-207 re-seed + polympc's dual carry-over) -- the guess_lam / sol_lam arguments."""

@@ -729,22 +729,22 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
         MPCB_PROF(1)
         MPCB_APHASE({ b_ft(c, ts, tid); MPCB_WSTAMP(1) });
         MPCB_PROF(2)
-        // the separator right-hand side (71 threads, latency bound) shares its barrier interval with t = W rhs_I; it comes
-        // second because its threads own the short (32-coefficient) W rows, the 49-coefficient rows set the interval's length
-        MPCB_APHASE_NS(b_w(c, ts, tid));
-        MPCB_APHASE_NS(b_seprhs(c, tid));
-        MPCB_APHASE({
-            const double o = MPCB_PEER(acc, 1);
-            ts.t = wrole<SH>(tid).paired ? ts.acc + o : ts.acc;
-            MPCB_WSTAMP(2)
-        });
+        MPCB_APHASE({ b_seprhs(c, tid); MPCB_WSTAMP(2) });
         MPCB_PROF(3)
+        // t = W rhs_I only reads rhs and is not needed before phase D.  It runs in the separator-solve interval, after that
+        // interval's own short critical chain (18 multiply-adds on 288 threads, two shuffles, the x~_B store): there it costs
+        // ~610 cycles per iteration; next to the separator rhs it cost ~910, next to F^T rhs_I ~935 (profiles/r1z_*)
         MPCB_APHASE_NS(c_separator(c, ts, tid));
         MPCB_APHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
-        MPCB_APHASE({
+        MPCB_APHASE_NS({
             const double s4 = ts.acc2 + MPCB_PEER(acc2, 2);
             const int cu = L::cunit(tid);
             if (cu >= 0 && (cu & 3) == 0) c.xt[L::sepidx(cu >> 2)] = s4;
+        });
+        MPCB_APHASE_NS(b_w(c, ts, tid));
+        MPCB_APHASE({
+            const double o = MPCB_PEER(acc, 1);
+            ts.t = wrole<SH>(tid).paired ? ts.acc + o : ts.acc;
             MPCB_WSTAMP(3)
         });
         MPCB_PROF(4)

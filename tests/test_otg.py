@@ -59,6 +59,36 @@ def test_profile_properties(kind, seed, margins):
     assert n_ok >= 48
 
 
+def test_blocked_intervals_and_near_zero_cruise():
+    """Synchronisation beyond the plain case: (i) a joint whose only way to last T is a cruise velocity far below the grid
+    spacing (tiny displacement, non-zero end velocity: problems 106 and 400 of the benchmark batch), (ii) a duration inside
+    a joint's blocked interval, where T must move to the end of the interval (status 1).  Every valid input gets a profile."""
+    lim = M.default_limits(BENCH_MARGINS)
+    x0, xT = M.generate_problems(lim, 0, 1, 1000)
+    for i in (106, 400):
+        rc, tr = M.otg_calculate(lim, x0[i], xT[i])
+        assert rc == 0
+        q, v, a = M.otg_at_time(tr, tr.T)
+        assert np.allclose(q, xT[i, :7], atol=1e-9) and np.allclose(v, xT[i, 7:], atol=1e-9)
+    assert all(M.otg_calculate(lim, x0[i], xT[i])[0] == 0 for i in range(0, 1000, 7))
+    lim = M.default_limits(OFFLINE_MARGINS)
+    vl = OFFLINE_MARGINS[1] * np.array(lim.vmax); al = OFFLINE_MARGINS[2] * np.array(lim.amax)
+    x0, xT = M.generate_problems(lim, 1, 7, 4000)
+    grown = 0
+    for i in range(4000):
+        rc, tr = M.otg_calculate(lim, x0[i], xT[i])
+        assert rc in (0, 1)
+        if rc == 1:
+            grown += 1
+            q, v, a = M.otg_at_time(tr, tr.T)
+            assert np.allclose(q, xT[i, :7], atol=1e-9) and np.allclose(v, xT[i, 7:], atol=1e-9) and np.allclose(a, 0, atol=1e-6)
+            assert np.allclose(np.array(tr.t).sum(axis=1), tr.T, rtol=0, atol=1e-9)
+            for s in np.linspace(0, 1, 57):
+                q, v, a = M.otg_at_time(tr, s * tr.T)
+                assert np.all(np.abs(v) <= vl * (1 + 1e-9)) and np.all(np.abs(a) <= al * (1 + 1e-9))
+    assert grown >= 1
+
+
 def test_guess_batch_samples_the_profile():
     lim = M.default_limits(BENCH_MARGINS); s = M.default_settings()
     x0, xT = M.generate_problems(lim, 0, 1, 8)

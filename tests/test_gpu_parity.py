@@ -53,6 +53,22 @@ def test_solve_matches_oracle(oracle, solver, kind, seed, margins, n):
     assert np.abs(o1[3] - slam[0]).max() < 1e-5 * max(1.0, np.abs(o1[3]).max())
 
 
+def test_full_benchmark_batch_matches_oracle(oracle, solver):
+    """BASELINE config 2 at its full size: all 1000 problems of the mpc_benchmark batch (seed 1) against the oracle --
+    identical status / iteration counts / line-search record for every problem, T within 1e-6 relative, nodes within 1e-5."""
+    import os
+    n = 1000
+    s, lim, x0, xT, gx, gu, gT = _problems(0, 1, n, BENCH_MARGINS)
+    solver.set_limits(lim)
+    sx, su, sT, _, st = solver.solve(x0, xT, gx, gu, gT)
+    so = oracle.default_settings(); lo = oracle.default_limits(BENCH_MARGINS)
+    osx, osu, oT, ost = oracle.solve_batch(so, lo, x0, xT, gx, gu, gT, nthreads=os.cpu_count() or 8)
+    assert np.all(np.abs(sT - oT) <= 1e-6 * np.abs(oT)), np.abs(sT - oT).max()
+    assert np.abs(sx - osx).max() < 1e-5 and np.abs(su - osu).max() < 1e-5, (np.abs(sx - osx).max(), np.abs(su - osu).max())
+    bad = [i for i in range(n) if _stats_tuple(st[i]) != _ostats_tuple(ost[i])]
+    assert not bad, bad[:10]
+
+
 def test_embedded_reference_problem(oracle, solver):
     """The one start/target pair the reference's notebook embeds, with its Ruckig samples as the guess."""
     import os

@@ -433,21 +433,23 @@ MPCB_DEV void b_ft(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     TmBuf<2> f2;
     const int so = L::tm_ft(tid);
     tm_ld(ts.tma(), so, f0); tm_ld(ts.tma(), so + 8, f1); tm_ld(ts.tma(), so + 16, f2);
-    tm_wait(f0, f1, f2);
     {
+        // the rhs chunk is read while the tensor-memory loads are in flight (the wait orders memory operations behind it)
         const double* b = c.rhs + L::ibase(f.seg) + f.r0;
+        d2 v[9];
+        MPCB_UNROLL
+        for (int i = 0; i < 9; i++) v[i] = ld2(b + 2 * i);
+        tm_wait(f0, f1, f2);
         double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
         MPCB_UNROLL
         for (int i = 0; i < 8; i += 4) {
-            const d2 v = ld2(b + i), v2 = ld2(b + i + 2);
-            a0 += f0.get(i) * v.a; a1 += f0.get(i + 1) * v.b; a2 += f0.get(i + 2) * v2.a; a3 += f0.get(i + 3) * v2.b;
+            a0 += f0.get(i) * v[i / 2].a; a1 += f0.get(i + 1) * v[i / 2].b; a2 += f0.get(i + 2) * v[i / 2 + 1].a; a3 += f0.get(i + 3) * v[i / 2 + 1].b;
         }
         MPCB_UNROLL
         for (int i = 0; i < 8; i += 4) {
-            const d2 v = ld2(b + 8 + i), v2 = ld2(b + 8 + i + 2);
-            a0 += f1.get(i) * v.a; a1 += f1.get(i + 1) * v.b; a2 += f1.get(i + 2) * v2.a; a3 += f1.get(i + 3) * v2.b;
+            a0 += f1.get(i) * v[4 + i / 2].a; a1 += f1.get(i + 1) * v[4 + i / 2].b; a2 += f1.get(i + 2) * v[5 + i / 2].a; a3 += f1.get(i + 3) * v[5 + i / 2].b;
         }
-        { const d2 v = ld2(b + 16); a0 += f2.get(0) * v.a; a1 += f2.get(1) * v.b; }
+        a0 += f2.get(0) * v[8].a; a1 += f2.get(1) * v[8].b;
         // the p column is summed through fpc (phase B') instead
         if (f.unit >= 0 && f.col < SH::nb(f.seg) - 1) c.partF[f.unit] = (a0 + a1) + (a2 + a3);
     }
@@ -543,18 +545,21 @@ MPCB_DEV void c_separator(ACtx<SH>& c, ATS<SH>& ts, int tid) {
         const int so = L::tm_c(tid);
         tm_ld(ts.tma(), so, c0); tm_ld(ts.tma(), so + 8, c1); tm_ld(ts.tma(), so + 16, c2);
         const double* rb = c.rB + (tid & 3);
+        double rv[18];                                   // read while the tensor-memory loads are in flight
+        MPCB_UNROLL
+        for (int jj = 0; jj < 18; jj++) rv[jj] = rb[4 * jj];
         tm_wait(c0, c1, c2);
         MPCB_UNROLL
         for (int jj = 0; jj < 8; jj += 4) {
-            a0 += c0.get(jj) * rb[4 * jj]; a1 += c0.get(jj + 1) * rb[4 * jj + 4];
-            a2 += c0.get(jj + 2) * rb[4 * jj + 8]; a3 += c0.get(jj + 3) * rb[4 * jj + 12];
+            a0 += c0.get(jj) * rv[jj]; a1 += c0.get(jj + 1) * rv[jj + 1];
+            a2 += c0.get(jj + 2) * rv[jj + 2]; a3 += c0.get(jj + 3) * rv[jj + 3];
         }
         MPCB_UNROLL
         for (int jj = 0; jj < 8; jj += 4) {
-            a0 += c1.get(jj) * rb[32 + 4 * jj]; a1 += c1.get(jj + 1) * rb[32 + 4 * jj + 4];
-            a2 += c1.get(jj + 2) * rb[32 + 4 * jj + 8]; a3 += c1.get(jj + 3) * rb[32 + 4 * jj + 12];
+            a0 += c1.get(jj) * rv[8 + jj]; a1 += c1.get(jj + 1) * rv[8 + jj + 1];
+            a2 += c1.get(jj + 2) * rv[8 + jj + 2]; a3 += c1.get(jj + 3) * rv[8 + jj + 3];
         }
-        a0 += c2.get(0) * rb[64]; a1 += c2.get(1) * rb[68];
+        a0 += c2.get(0) * rv[16]; a1 += c2.get(1) * rv[17];
     }
     ts.acc = (a0 + a1) + (a2 + a3);
 }

@@ -492,14 +492,13 @@ MPCB_DEV void b_w(ACtx<SH>& c, ATS<SH>& ts, int tid) {
         TmBuf<8> w0, w1;                               // columns 32..47 of the row
         TmBuf<1> w2;                                   // column 48
         const int so = L::tm_wov(tid);
-        tm_ld(ts.tma(), so, w0);
+        tm_ld(ts.tma(), so, w0); tm_ld(ts.tma(), so + 8, w1); tm_ld(ts.tma(), so + 16, w2);    // in flight during the register part
         double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
         MPCB_UNROLL
         for (int e = 0; e < L::WREG; e += 4) {
             const d2 v = ld2(b + e), v2 = ld2(b + e + 2);
             a0 += ts.wreg[e] * v.a; a1 += ts.wreg[e + 1] * v.b; a2 += ts.wreg[e + 2] * v2.a; a3 += ts.wreg[e + 3] * v2.b;
         }
-        tm_ld(ts.tma(), so + 8, w1); tm_ld(ts.tma(), so + 16, w2);
         tm_wait(w0, w1, w2);
         MPCB_UNROLL
         for (int e = 0; e < 8; e += 4) {

@@ -37,9 +37,9 @@ W_FAC = 63 * 78 ** 2 + 4 * 49 * 78 ** 2 + 70 * 85 ** 2 + 71 ** 3 + 120000   # sw
 W_LIN = 300000                                            # 19 x (RNEA derivatives + CRBA + frame Jacobian) + collocation
 W_MERIT = 35000                                           # 19 x (RNEA + FK) + residuals
 # DRAM bytes of one admm_kernel launch per OCP, from the committed ncu --set full capture of this command
-# (profiles/r1f_admm_kernel_raw.csv: dram__bytes_read.sum 472.52 MB + dram__bytes_write.sum 12.33 MB for 1000 OCPs):
+# (profiles/r1g_admm_kernel_raw.csv: dram__bytes_read.sum 472.73 MB + dram__bytes_write.sum 12.66 MB for 1000 OCPs):
 # the factorised QP block (W, F, C^-1 strips and the Jacobian image, ~505 KB per OCP) is read once per QP.
-NCU_ADMM_DRAM_BYTES_PER_OCP = (472.523776e6 + 12.325632e6) / 1000
+NCU_ADMM_DRAM_BYTES_PER_OCP = (472.734976e6 + 12.664320e6) / 1000
 
 
 def flops_of(stats):
@@ -245,7 +245,7 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "clocks": clk.summary(),
         "roofline": {"bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s", "frac": achieved / fp64_peak if fp64_peak > 0 else None,
-                     "traffic": NCU_ADMM_DRAM_BYTES_PER_OCP * B, "traffic_source": "ncu --set full, profiles/r1f_admm_kernel_raw.csv (dram read + write of one admm_kernel launch, scaled to the batch)",
+                     "traffic": NCU_ADMM_DRAM_BYTES_PER_OCP * B, "traffic_source": "ncu --set full, profiles/r1g_admm_kernel_raw.csv (dram read + write of one admm_kernel launch, scaled to the batch)",
                      "peak_source": "FP64 FMA micro-benchmark run in this process (MEASURED_PEAKS.json has no FP64 figure)",
                      "kernel": "admm_kernel", "flops_per_launch": flops_admm_launch, "kernel_ms": admm_ms_launch,
                      "kernel_share_of_step": sum(admm_ms) / ms_total,

@@ -126,6 +126,38 @@ def test_device_generator_matches_host(solver, kind, seed, margins):
     assert np.array_equal(p0, d0[1500:1800]) and np.array_equal(pT, dT[1500:1800])
 
 
+def test_device_resident_pipeline(solver):
+    """generate -> warm start -> solve with device pointers only (torch tensors; a non-default stream) gives what the
+    host-pointer calls give for the same problems."""
+    import torch
+    n = 40
+    lim = M.default_limits(BENCH_MARGINS)
+    solver.set_limits(lim)
+    dev = torch.device("cuda:0")
+    f64 = dict(dtype=torch.float64, device=dev)
+    N = solver.N
+    dx0 = torch.empty(n, 14, **f64); dxT = torch.empty(n, 14, **f64)
+    dgx = torch.empty(n, 14 * N, **f64); dgu = torch.empty(n, 7 * N, **f64); dgT = torch.empty(n, **f64)
+    dsx = torch.empty_like(dgx); dsu = torch.empty_like(dgu); dsT = torch.empty_like(dgT)
+    dst = torch.zeros(n * M.capi.STATS_DTYPE.itemsize, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+    with torch.cuda.stream(stream):
+        sp = stream.cuda_stream
+        solver.generate_device(0, 5, n, dx0.data_ptr(), dxT.data_ptr(), first=100, stream=sp)
+        solver.guess_device(n, dx0.data_ptr(), dxT.data_ptr(), dgx.data_ptr(), dgu.data_ptr(), dgT.data_ptr(), stream=sp)
+        solver.solve_device(n, dx0.data_ptr(), dxT.data_ptr(), dgx.data_ptr(), dgu.data_ptr(), dgT.data_ptr(), 0, dsx.data_ptr(), dsu.data_ptr(),
+                            dsT.data_ptr(), 0, dst.data_ptr(), stream=sp)
+    stream.synchronize()
+    x0 = dx0.cpu().numpy(); xT = dxT.cpu().numpy()
+    h0, hT = M.generate_problems(lim, 0, 5, 140)
+    assert np.abs(x0 - h0[100:]).max() < 1e-13 and np.abs(xT - hT[100:]).max() < 1e-9
+    # the same device-made problems and guesses through the host-pointer entry point: bitwise the same solution
+    sx, su, sT, _, st = solver.solve(x0, xT, dgx.cpu().numpy(), dgu.cpu().numpy(), dgT.cpu().numpy())
+    assert np.array_equal(sx, dsx.cpu().numpy()) and np.array_equal(su, dsu.cpu().numpy()) and np.array_equal(sT, dsT.cpu().numpy())
+    dstats = np.frombuffer(dst.cpu().numpy().tobytes(), dtype=M.capi.STATS_DTYPE)
+    assert np.array_equal(dstats["status"], st["status"]) and np.array_equal(dstats["qp_iters_total"], st["qp_iters_total"])
+
+
 def test_receding_horizon_resolve(oracle, solver):
     """BASELINE config 5: re-solve 1 ms later, warm-started from the previous solution INCLUDING its multipliers
     (motionPlanner.cpp:199-207 re-seed + polympc's dual carry-over) -- the guess_lam / sol_lam arguments."""

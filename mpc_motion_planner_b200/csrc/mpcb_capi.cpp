@@ -21,6 +21,8 @@ struct mpcb_handle {
     mpcb_limits lim;
     KernelConst kc;
     int grid_max = 0;
+    ShapeInfo si;
+    double* d_gmat = nullptr;            // per-CTA matrix blocks of the larger collocation shapes (ShapeInfo::gmat_doubles each)
     int* d_counter = nullptr;            // one work counter per kernel launch of a chunk
     int n_counter = 0;
     double* d_workspace = nullptr;       // per-OCP blocks (iterate, multipliers, QP block) of one chunk
@@ -86,13 +88,15 @@ int mpcb_create(const mpcb_settings* s, int device, mpcb_handle** out) {
     cudaDeviceProp prop;
     if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return fail("cudaGetDeviceProperties", e);
     h->sm_count = prop.multiProcessorCount;
-    if ((size_t)prop.sharedMemPerBlockOptin < solve_smem_bytes()) {
+    if ((e = shape_info(s->poly_order, s->num_seg, &h->si)) != cudaSuccess) return fail("shape_info", e);
+    if ((size_t)prop.sharedMemPerBlockOptin < (h->si.stage_smem > h->si.admm_smem ? h->si.stage_smem : h->si.admm_smem)) {
         g_create_error = "device offers too little opt-in shared memory per block for the OCP kernel";
         mpcb_destroy(h);
         return MPCB_ERR_UNSUPPORTED;
     }
-    if ((e = solve_prepare()) != cudaSuccess) return fail("cudaFuncSetAttribute(solve kernels)", e);
+    if ((e = solve_prepare(s->poly_order, s->num_seg)) != cudaSuccess) return fail("cudaFuncSetAttribute(solve kernels)", e);
     h->grid_max = h->sm_count;      // one CTA per SM (shared memory bound)
+    if (h->si.gmat_doubles && (e = cudaMalloc(&h->d_gmat, sizeof(double) * h->si.gmat_doubles * (size_t)h->grid_max)) != cudaSuccess) return fail("cudaMalloc(matrix blocks)", e);
     if ((e = cudaMalloc(&h->d_prof, 512 * sizeof(long long))) != cudaSuccess || (e = cudaMemset(h->d_prof, 0, 512 * sizeof(long long))) != cudaSuccess) return fail("cudaMalloc(prof)", e);
     if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
     *out = h;
@@ -105,6 +109,7 @@ void mpcb_destroy(mpcb_handle* h) {
     if (h->d_counter) cudaFree(h->d_counter);
     if (h->d_workspace) cudaFree(h->d_workspace);
     if (h->d_stage) cudaFree(h->d_stage);
+    if (h->d_gmat) cudaFree(h->d_gmat);
     if (h->d_prof) cudaFree(h->d_prof);
     for (cudaEvent_t e : h->kev) cudaEventDestroy(e);
     if (h->ev0) cudaEventDestroy(h->ev0);
@@ -137,7 +142,7 @@ static const int CHUNK_MAX = 4096;
 static int ensure_workspace(mpcb_handle* h, int ocps, int counters) {
     if (ocps > h->ws_ocps) {
         if (h->d_workspace) { cudaFree(h->d_workspace); h->d_workspace = nullptr; h->ws_ocps = 0; }
-        cudaError_t e = cudaMalloc(&h->d_workspace, sizeof(double) * solve_workspace_doubles_per_ocp() * (size_t)ocps);
+        cudaError_t e = cudaMalloc(&h->d_workspace, sizeof(double) * h->si.ws_doubles * (size_t)ocps);
         if (e != cudaSuccess) { h->err = std::string("cudaMalloc(workspace): ") + cudaGetErrorString(e); return MPCB_ERR_ALLOC; }
         h->ws_ocps = ocps;
     }
@@ -209,12 +214,20 @@ int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, 
     const int n_launch = 2 + 3 * h->st.sqp_max_iter;               // persistent kernels (one work counter each) per chunk
     { int rc = ensure_workspace(h, chunk, n_launch); if (rc) return rc; }
     h->kused = 0;
+    const bool debug_sync = getenv("MPCB_DEBUG_SYNC") != nullptr;      // debugging aid: synchronise after every launch and name the failing kernel
     CK(cudaEventRecord(h->ev0, stream));
 #define TIMED(kind_, call_)                                                                                        \
     do {                                                                                                           \
         if (timed_launch_begin(h, kind_, stream)) { h->err = "cudaEventRecord failed"; return MPCB_ERR_CUDA; }     \
         CK(call_);                                                                                                 \
         timed_launch_end(h, stream);                                                                               \
+        if (debug_sync) {                                                                                          \
+            cudaError_t se_ = cudaStreamSynchronize(stream);                                                       \
+            if (se_ != cudaSuccess) {                                                                              \
+                h->err = std::string(#call_) + " [kernel]: " + cudaGetErrorString(se_);                            \
+                return MPCB_ERR_CUDA;                                                                              \
+            }                                                                                                      \
+        }                                                                                                          \
     } while (0)
     for (int c0 = 0; c0 < n; c0 += chunk) {
         const int nn = (n - c0) < chunk ? (n - c0) : chunk;
@@ -228,13 +241,19 @@ int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, 
         CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int) * n_launch, stream));
         int li = 0;
         // load -> [node Jacobians -> linearise/factorise -> ADMM -> node trial values -> line search/step] x sqp_max_iter
-        TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 0, 0, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
+        // (the shape-generic / adaptive-rho path runs linearise + factorise + ADMM as one kernel, accounted as the ADMM kind)
+        const bool generic = settings_generic_path(&h->st) != 0;
+        TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 0, 0, grid, h->d_counter + li++, h->d_workspace, h->d_gmat, h->d_prof, stream));
         for (int it = 1; it <= h->st.sqp_max_iter; it++) {
-            TIMED(MPCB_KERNEL_NODE, launch_node_jac(nn, h->d_workspace, stream));
-            TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 1, it, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
-            TIMED(MPCB_KERNEL_ADMM, launch_admm(h->kc, nn, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
+            TIMED(MPCB_KERNEL_NODE, launch_node_jac(h->kc, nn, h->d_workspace, stream));
+            if (generic) {
+                TIMED(MPCB_KERNEL_ADMM, launch_sqp_stage(h->kc, cp, nn, 3, it, grid, h->d_counter + li++, h->d_workspace, h->d_gmat, h->d_prof, stream));
+            } else {
+                TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 1, it, grid, h->d_counter + li++, h->d_workspace, h->d_gmat, h->d_prof, stream));
+                TIMED(MPCB_KERNEL_ADMM, launch_admm(h->kc, nn, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
+            }
             TIMED(MPCB_KERNEL_NODE, launch_node_val(h->kc, nn, h->d_workspace, stream));
-            TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 2, it, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
+            TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 2, it, grid, h->d_counter + li++, h->d_workspace, h->d_gmat, h->d_prof, stream));
         }
     }
 #undef TIMED

@@ -16,14 +16,14 @@
 
 namespace mpcb {
 
-constexpr int NT = 512;   // threads per CTA
+constexpr int NT = 512;   // threads per CTA of the (3,6) kernels (mpcb_admm.h, mpcb_export.h); the stage phases use SH::NT
 
 #ifdef MPCB_EMUL
 #define MPCB_DEV inline
 #define MPCB_DRIVER_PARAMS(SH) Ctx<SH>& c, TS<SH>* tsv
 #define MPCB_DRIVER_ARGS c, tsv
 #define MPCB_PHASE(...)                       \
-    for (int tid = 0; tid < NT; ++tid) {      \
+    for (int tid = 0; tid < SH::NT; ++tid) {  \
         auto& ts = tsv[tid];                  \
         (void)ts;                             \
         __VA_ARGS__;                          \
@@ -73,16 +73,33 @@ enum {
     SC_COUNT = 24
 };
 // uniform int scalars
-enum { IS_QP_DONE = 0, IS_QP_STATUS, IS_QP_ITERS, IS_LS_ACCEPT, IS_SQP_DONE, IS_COUNT = 8 };
+enum { IS_QP_DONE = 0, IS_QP_STATUS, IS_QP_ITERS, IS_LS_ACCEPT, IS_SQP_DONE, IS_NEXT = 7 /* the persistent CTA's next problem index */, IS_COUNT = 8 };
 // atomic-max slots
 enum { UM_RP = 0, UM_RD, UM_NAX, UM_NX, UM_NZ, UM_NHX, UM_NATY, UM_NH, UM_A, UM_B, UM_V, UM_COUNT = 12 };
 
+// Tiling of the symmetric sweeps (mpcb_qp.h): 5 x 5 register tiles of the lower triangle, one thread per tile.
+template <class SH>
+struct Sweep {
+    static constexpr int TILE = 5;
+    static constexpr int tiles(int M) { return ((M + TILE - 1) / TILE) * ((M + TILE - 1) / TILE + 1) / 2; }
+    static constexpr int MAXM = SH::AUGMAX > SH::NB ? SH::AUGMAX : SH::NB;
+    static constexpr int COLS = ((MAXM + TILE - 1) / TILE * TILE + 1 + 7) / 8 * 8;     // one published column + 1/pivot in the last slot
+    static constexpr int SLOT_I = tiles(SH::AUGMAX), SLOT_C = tiles(SH::NB);           // threads per interior matrix / for the separator
+    static constexpr int PAR0 = SH::NT / SLOT_I;
+    static constexpr int PAR = PAR0 > SH::NS ? SH::NS : (PAR0 > 6 ? 6 : PAR0);          // interior matrices swept per round
+    static_assert(SLOT_I <= SH::NT && SLOT_C <= SH::NT && PAR >= 1, "sweep tiling: one thread per 5 x 5 tile of the largest matrix");
+};
+
 template <class SH>
 struct Layout {   // offsets in doubles into the dynamic shared-memory block
-    static constexpr int MAT = 0;                                  // W | F | C   (also: derivative scratch, QP result)
+    // The matrix area (W | F | C | BB) sits in shared memory when it fits (the base shape); for the larger collocation shapes
+    // it lives in a per-CTA block of global memory (Ctx::bind gets the pointer) and only vectors + Jacobians stay on chip.
+    static constexpr bool GMAT = (SH::MATSIZE + SH::BBSIZE) > 22000;
+    static constexpr int MATDOUBLES = SH::MATSIZE + SH::BBSIZE;
+    static constexpr int MAT = 0;                                  // W | F | C   (also: QP result)
     static constexpr int W = MAT, F = W + SH::WSIZE, C = F + SH::FSIZE;
     static constexpr int BB = MAT + SH::MATSIZE;
-    static constexpr int JG = BB + SH::BBSIZE;
+    static constexpr int JG = GMAT ? 0 : BB + SH::BBSIZE;
     static constexpr int VW = JG + SH::NN * 8 * 22;                // w      (rows)
     static constexpr int VRHS = VW + SH::VP;                       // rhs    (vars; rows in the residual check)
     static constexpr int VXT = VRHS + SH::VP;                      // x~     (vars)
@@ -90,17 +107,22 @@ struct Layout {   // offsets in doubles into the dynamic shared-memory block
     static constexpr int PCOL = HA + SH::VP;                       // A[:, p] of the equality rows
     static constexpr int PART = PCOL + SH::NEQ;                    // F^T rhs partials
     static constexpr int PSUM = PART + SH::PARTSIZE + 1;           // 2 x 32 partial sums
-    static constexpr int COLBUF = PSUM + 64;                       // NS pivot columns
-    static constexpr int COLSTRIDE = (SH::AUGMAX + 7) / 8 * 8;
-    static constexpr int LIMS = COLBUF + (SH::NS > 1 ? SH::NS : 1) * COLSTRIDE;   // per-joint bounds 5x7 + 5, x0, xT
+    static constexpr int COLBUF = (PSUM + 64 + 1) / 2 * 2;         // 2 x PAR published pivot columns
+    static constexpr int LIMS = COLBUF + 2 * Sweep<SH>::PAR * Sweep<SH>::COLS;   // per-joint bounds 5x7 + 5, x0, xT
     static constexpr int SCAL = LIMS + 72;
     static constexpr int UMAX = SCAL + SC_COUNT;
     static constexpr int ISC = UMAX + UM_COUNT;
     static constexpr int TOTAL = ISC + IS_COUNT;                   // ints stored in 8-byte slots for simplicity
     static constexpr size_t BYTES = (size_t)TOTAL * 8;
-    static constexpr int DERIV_STRIDE = (int)(sizeof(rbd::DerivScratch) / 8) + 1;
-    static_assert(SH::NN * DERIV_STRIDE <= SH::MATSIZE + SH::BBSIZE, "derivative scratch must fit the matrix area");
     static_assert(SH::NDUAL + SH::VP <= SH::MATSIZE, "QP result must fit the matrix area");
+    static_assert(BYTES <= 227 * 1024, "shared-memory block of the stage kernel exceeds 227 KB");
+};
+// Result block of one QP in global memory (per OCP): step p (kernel order, VP) | multipliers (NDUAL + 4) | info (4).
+// The base shape embeds it in the ADMM kernel's QP block (specialisation in mpcb_export.h).
+template <class SH>
+struct QBL {
+    static constexpr int G_RES = 0, R_LAM = SH::VP, R_INFO = SH::VP + SH::NDUAL + 4;
+    static constexpr int QPBLOCK = G_RES + R_INFO + 4;
 };
 // LIMS sub-offsets
 enum { LM_QLO = 0, LM_QHI = 7, LM_V = 14, LM_A = 21, LM_TAU = 28, LM_MINH = 35, LM_EPS, LM_PLB, LM_PUB, LM_X0 = 40, LM_XT = 54 };
@@ -124,15 +146,17 @@ struct Ctx {
     // results of the last QP, aliased onto the matrix area after the ADMM loop
     double* qp_p;                  // step p, kernel order
     double* qp_lam;                // QP multipliers
-    MPCB_HD void bind(double* smem) {
+    // gmat: this CTA's matrix block in global memory (Layout::MATDOUBLES doubles), used when Layout::GMAT
+    MPCB_HD void bind(double* smem, double* gmat = nullptr) {
         typedef Layout<SH> L;
         sm = smem;
-        W = sm + L::W; F = sm + L::F; C = sm + L::C; BB = sm + L::BB; Jg = sm + L::JG; w = sm + L::VW; rhs = sm + L::VRHS;
+        double* mat = L::GMAT ? gmat : sm + L::MAT;
+        W = mat; F = mat + SH::WSIZE; C = F + SH::FSIZE; BB = mat + SH::MATSIZE; Jg = sm + L::JG; w = sm + L::VW; rhs = sm + L::VRHS;
         xt = sm + L::VXT; Ha = sm + L::HA; pcol = sm + L::PCOL; part = sm + L::PART; psum = sm + L::PSUM;
         colbuf = sm + L::COLBUF; lims = sm + L::LIMS; scal = sm + L::SCAL;
         umax = reinterpret_cast<unsigned long long*>(sm + L::UMAX);
         isc = reinterpret_cast<long long*>(sm + L::ISC);
-        qp_p = sm + L::MAT; qp_lam = sm + L::MAT + SH::VP;
+        qp_p = mat; qp_lam = mat + SH::VP;
     }
 };
 

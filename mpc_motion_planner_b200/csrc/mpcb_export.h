@@ -9,6 +9,12 @@
 
 namespace mpcb {
 
+template <>
+struct QBL<Shape<3, 6>> {
+    typedef AL<Shape<3, 6>> L;
+    static constexpr int G_RES = L::G_RES, R_LAM = L::R_LAM, R_INFO = L::R_INFO, QPBLOCK = L::QPBLOCK;
+};
+
 template <class SH>
 MPCB_DEV double sym_packed(const double* P, int i, int j) {
     const int hi = i > j ? i : j, lo = i > j ? j : i;
@@ -123,10 +129,10 @@ MPCB_DEV void export_qp(MPCB_DRIVER_PARAMS(SH), double* qb) {
 // QP result (kernel order) -> the shared-memory slots the SQP stage reads (aliased onto the dead factor)
 template <class SH>
 MPCB_DEV void import_qp(Ctx<SH>& c, int tid, const double* qb) {
-    typedef AL<SH> L;
+    typedef QBL<SH> L;
     const double* res = qb + L::G_RES;
     if (tid < SH::NVAR) c.qp_p[tid] = res[tid];
-    for (int i = tid; i < SH::NDUAL; i += NT) c.qp_lam[i] = res[L::R_LAM + i];
+    for (int i = tid; i < SH::NDUAL; i += SH::NT) c.qp_lam[i] = res[L::R_LAM + i];
     if (tid == 0) { c.isc[IS_QP_STATUS] = (long long)res[L::R_INFO]; c.isc[IS_QP_ITERS] = (long long)res[L::R_INFO + 1]; }
 }
 

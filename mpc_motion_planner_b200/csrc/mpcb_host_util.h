@@ -37,11 +37,18 @@ inline void fill_limtab(const mpcb_limits* lim, double* t) {
     t[35] = lim->min_height; t[36] = lim->final_eps; t[37] = lim->p_lb; t[38] = lim->p_ub; t[39] = 0;
 }
 inline int settings_supported(const mpcb_settings* s, const char** why) {
-    if (s->qp_adaptive_rho) { *why = "qp_adaptive_rho=1 is not implemented by the kernels"; return 0; }
+    if (s->qp_adaptive_rho && !(s->qp_adaptive_rho_tolerance > 1.0)) { *why = "qp_adaptive_rho_tolerance must be > 1"; return 0; }
     if (s->sqp_max_iter < 1 || s->qp_max_iter < 1 || s->line_search_max_iter < 1) { *why = "iteration limits must be >= 1"; return 0; }
     if (s->line_search_max_iter > 15) { *why = "line_search_max_iter must be <= 15 (trial-point workspace)"; return 0; }
-    if (!(s->poly_order == 3 && s->num_seg == 6)) { *why = "only (poly_order, num_seg) = (3, 6) is instantiated"; return 0; }
+    const int po = s->poly_order, ns = s->num_seg;
+    if (!((po == 3 && (ns == 6 || ns == 12)) || (po == 5 && ns == 6) || (po == 7 && ns == 4))) {
+        *why = "(poly_order, num_seg) must be one of the instantiated shapes (3,6), (3,12), (5,6), (7,4)";
+        return 0;
+    }
     return 1;
 }
+
+// which solve path a settings struct takes: the (3,6) register/TMEM ADMM kernel, or the shape-generic fused stage (mpcb_gadmm.h)
+inline int settings_generic_path(const mpcb_settings* s) { return !(s->poly_order == 3 && s->num_seg == 6) || s->qp_adaptive_rho != 0; }
 
 }  // namespace mpcb

@@ -23,7 +23,7 @@ template <class SH>
 struct WS {
     static constexpr int Z = 0, LAM = SH::VP, FLAGS = LAM + SH::NDUAL + 8, JG = FLAGS + 4, GJ = JG + SH::NN * 176, GVAL = GJ + SH::NINEQ;
     static constexpr int QB = GVAL + MAX_TRIALS * SH::NINEQ;
-    static constexpr size_t STRIDE = (size_t)QB + AL<SH>::QPBLOCK;
+    static constexpr size_t STRIDE = (size_t)QB + QBL<SH>::QPBLOCK;
 };
 
 template <class SH>
@@ -41,16 +41,22 @@ __device__ __forceinline__ void bind_problem(Ctx<SH>& c, Problem& pb, const Kern
     pb.stats = bp.stats ? bp.stats + i : nullptr;
 }
 
-// SQP stage kernel: kind 0 = stage_load, 1 = stage_linfac, 2 = stage_lsstep of SQP iteration `it`
-template <class SH>
-__global__ void __launch_bounds__(NT, 1)
+// SQP stage kernel: kind 0 = stage_load, 1 = stage_linfac, 2 = stage_lsstep of SQP iteration `it`, 3 = stage_qp_generic (linearise,
+// factorise and the ADMM iterations in one kernel: larger collocation shapes, adaptive rho).  gmat: one matrix block per CTA for the
+// shapes whose KKT inverses do not fit shared memory (Layout::GMAT).
+// GEN selects the kernel that holds kind 3 only, so that the code generation of the three light stages does not change with it.
+template <class SH, bool GEN>
+__global__ void __launch_bounds__(SH::NT, 1)
 sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, const int n, const int kind, const int it,
-                 int* __restrict__ counter, double* __restrict__ workspace, long long* prof) {
+                 int* __restrict__ counter, double* __restrict__ workspace, double* __restrict__ gmat, long long* prof) {
+    // (no static __shared__ variable next to the dynamic block: with two shared bases in one kernel ptxas 12.9 rematerialised the
+    // dynamic base wrongly in the register-starved 1024-thread instances -- `ULEA URa, URb, URb, 0x18` -- and the CTA faulted;
+    // tests/test_capi_cpu.py::test_no_miscompiled_shared_base greps the SASS for that pattern)
     extern __shared__ double smem[];
-    __shared__ int s_next;
     const int tid = threadIdx.x;
     Ctx<SH> c;
-    c.bind(smem);
+    c.bind(smem, Layout<SH>::GMAT ? gmat + (size_t)blockIdx.x * Layout<SH>::MATDOUBLES : nullptr);
+    volatile long long& s_next = *reinterpret_cast<volatile long long*>(c.isc + IS_NEXT);
     c.st = &kc.st;
     c.cheb = &kc.cheb;
     c.prof = prof;
@@ -59,7 +65,7 @@ sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, con
     for (;;) {
         if (tid == 0) s_next = atomicAdd(counter, 1);
         __syncthreads();
-        const int i = s_next;
+        const int i = (int)s_next;
         __syncthreads();
         if (i >= n) break;
         double* ws = workspace + WS<SH>::STRIDE * i;
@@ -67,9 +73,13 @@ sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, con
         if (kind != 0 && flags[0]) continue;        // finished in an earlier SQP iteration
         Problem pb;
         bind_problem(c, pb, kc, bp, ws, i);
-        if (kind == 0) stage_load<SH>(c, ts, tid, pb, flags);
-        else if (kind == 1) stage_linfac<SH>(c, ts, tid, pb, ws + WS<SH>::QB);
-        else stage_lsstep<SH>(c, ts, tid, pb, ws + WS<SH>::QB, flags, it);
+        if constexpr (GEN) {
+            stage_qp_generic<SH>(c, ts, tid, pb, ws + WS<SH>::QB);
+        } else {
+            if (kind == 0) stage_load<SH>(c, ts, tid, pb, flags);
+            else if (kind == 1) { if constexpr (SH::PO == 3 && SH::NS == 6) stage_linfac<SH>(c, ts, tid, pb, ws + WS<SH>::QB); }
+            else stage_lsstep<SH>(c, ts, tid, pb, ws + WS<SH>::QB, flags, it);
+        }
     }
 }
 
@@ -99,7 +109,7 @@ node_val_kernel(const int n, const int ntrial, const double tau, double* __restr
     double* ws = workspace + WS<SH>::STRIDE * i;
     if (reinterpret_cast<const int*>(ws + WS<SH>::FLAGS)[0]) return;
     double g[8];
-    node_val<SH>(ws + WS<SH>::Z, ws + WS<SH>::QB + AL<SH>::G_RES, t, tau, k, g);
+    node_val<SH>(ws + WS<SH>::Z, ws + WS<SH>::QB + QBL<SH>::G_RES, t, tau, k, g);
     for (int j = 0; j < 8; j++) ws[WS<SH>::GVAL + (t * SH::NN + k) * 8 + j] = g[j];
 }
 
@@ -323,30 +333,68 @@ __global__ void fp64_peak_kernel(double* out, int iters) {
 }
 
 // ---- launchers -------------------------------------------------------------------------------------------------------
+// Instantiated collocation shapes (POLY_ORDER, NUM_SEG): the reference's (3,6) and BASELINE config 4's (3,12), (5,6), (7,4).
 typedef Shape<3, 6> SH36;
+#define MPCB_FOR_SHAPE(po, ns, ...)                                                           \
+    do {                                                                                      \
+        if ((po) == 3 && (ns) == 6) { typedef Shape<3, 6> SH; __VA_ARGS__; }                  \
+        else if ((po) == 3 && (ns) == 12) { typedef Shape<3, 12> SH; __VA_ARGS__; }           \
+        else if ((po) == 5 && (ns) == 6) { typedef Shape<5, 6> SH; __VA_ARGS__; }             \
+        else if ((po) == 7 && (ns) == 4) { typedef Shape<7, 4> SH; __VA_ARGS__; }             \
+        else return cudaErrorInvalidValue;                                                    \
+    } while (0)
 
-size_t solve_smem_bytes() { return Layout<SH36>::BYTES > AL<SH36>::BYTES ? Layout<SH36>::BYTES : AL<SH36>::BYTES; }
-size_t solve_workspace_doubles_per_ocp() { return WS<SH36>::STRIDE; }
-
-cudaError_t solve_prepare() {
-    cudaError_t e = cudaFuncSetAttribute(sqp_stage_kernel<SH36>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Layout<SH36>::BYTES);
+template <class SH>
+static size_t admm_smem_of() {
+    if constexpr (SH::PO == 3 && SH::NS == 6) return AL<SH>::BYTES;
+    else return 0;
+}
+template <class SH>
+static cudaError_t prepare_shape() {
+    cudaError_t e = cudaFuncSetAttribute(sqp_stage_kernel<SH, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Layout<SH>::BYTES);
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(admm_kernel<SH36>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AL<SH36>::BYTES);
+    e = cudaFuncSetAttribute(sqp_stage_kernel<SH, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Layout<SH>::BYTES);
+    if (e != cudaSuccess) return e;
+    if constexpr (SH::PO == 3 && SH::NS == 6) e = cudaFuncSetAttribute(admm_kernel<SH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AL<SH>::BYTES);
+    return e;
+}
+
+int shape_supported(int po, int ns) { return (po == 3 && (ns == 6 || ns == 12)) || (po == 5 && ns == 6) || (po == 7 && ns == 4); }
+
+cudaError_t shape_info(int po, int ns, ShapeInfo* si) {
+    MPCB_FOR_SHAPE(po, ns, {
+        si->stage_smem = Layout<SH>::BYTES; si->stage_threads = SH::NT; si->ws_doubles = WS<SH>::STRIDE;
+        si->gmat_doubles = Layout<SH>::GMAT ? (size_t)Layout<SH>::MATDOUBLES : 0;
+        si->admm_smem = admm_smem_of<SH>();
+    });
+    return cudaSuccess;
+}
+
+cudaError_t solve_prepare(int po, int ns) {
+    MPCB_FOR_SHAPE(po, ns, return prepare_shape<SH>());
+    return cudaSuccess;
 }
 cudaError_t launch_sqp_stage(const KernelConst& kc, const BatchPtrs& bp, int n, int kind, int it, int grid, int* counter, double* workspace,
-                             long long* prof, cudaStream_t stream) {
-    sqp_stage_kernel<SH36><<<grid, NT, Layout<SH36>::BYTES, stream>>>(kc, bp, n, kind, it, counter, workspace, prof);
+                             double* gmat, long long* prof, cudaStream_t stream) {
+    MPCB_FOR_SHAPE(kc.st.poly_order, kc.st.num_seg, {
+        if (kind == 3) sqp_stage_kernel<SH, true><<<grid, SH::NT, Layout<SH>::BYTES, stream>>>(kc, bp, n, kind, it, counter, workspace, gmat, prof);
+        else sqp_stage_kernel<SH, false><<<grid, SH::NT, Layout<SH>::BYTES, stream>>>(kc, bp, n, kind, it, counter, workspace, gmat, prof);
+    });
     return cudaGetLastError();
 }
-cudaError_t launch_node_jac(int n, double* workspace, cudaStream_t stream) {
-    const long long threads = (long long)n * SH36::NN;
-    node_jac_kernel<SH36><<<(unsigned)((threads + NODE_NT - 1) / NODE_NT), NODE_NT, 0, stream>>>(n, workspace);
+cudaError_t launch_node_jac(const KernelConst& kc, int n, double* workspace, cudaStream_t stream) {
+    MPCB_FOR_SHAPE(kc.st.poly_order, kc.st.num_seg, {
+        const long long threads = (long long)n * SH::NN;
+        node_jac_kernel<SH><<<(unsigned)((threads + NODE_NT - 1) / NODE_NT), NODE_NT, 0, stream>>>(n, workspace);
+    });
     return cudaGetLastError();
 }
 cudaError_t launch_node_val(const KernelConst& kc, int n, double* workspace, cudaStream_t stream) {
     const int ntrial = kc.st.line_search_max_iter + 1;
-    const long long threads = (long long)n * ntrial * SH36::NN;
-    node_val_kernel<SH36><<<(unsigned)((threads + NODE_NT - 1) / NODE_NT), NODE_NT, 0, stream>>>(n, ntrial, kc.st.sqp_tau, workspace);
+    MPCB_FOR_SHAPE(kc.st.poly_order, kc.st.num_seg, {
+        const long long threads = (long long)n * ntrial * SH::NN;
+        node_val_kernel<SH><<<(unsigned)((threads + NODE_NT - 1) / NODE_NT), NODE_NT, 0, stream>>>(n, ntrial, kc.st.sqp_tau, workspace);
+    });
     return cudaGetLastError();
 }
 cudaError_t launch_admm(const KernelConst& kc, int n, int grid, int* counter, double* workspace, long long* prof, cudaStream_t stream) {
@@ -356,9 +404,11 @@ cudaError_t launch_admm(const KernelConst& kc, int n, int grid, int* counter, do
 cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double* su, const double* sT, const double* target, int npts,
                           double* traj, mpcb_account* acc, int n, int grid, cudaStream_t stream) {
     const size_t smem = (size_t)29 * (npts + 1) * sizeof(double);
-    cudaError_t e = cudaFuncSetAttribute(sample_kernel<SH36>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    sample_kernel<SH36><<<grid, SAMPLE_NT, smem, stream>>>(kc, sx, su, sT, target, npts, traj, acc, n);
+    MPCB_FOR_SHAPE(kc.st.poly_order, kc.st.num_seg, {
+        cudaError_t e = cudaFuncSetAttribute(sample_kernel<SH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        sample_kernel<SH><<<grid, SAMPLE_NT, smem, stream>>>(kc, sx, su, sT, target, npts, traj, acc, n);
+    });
     return cudaGetLastError();
 }
 cudaError_t launch_otg_guess(const OtgConst& oc, int n, const double* x0, const double* xT, double* gx, double* gu, double* gT, cudaStream_t stream) {

@@ -28,14 +28,22 @@ struct BatchPtrs {
     mpcb_stats* stats;
 };
 
-size_t solve_smem_bytes();
-size_t solve_workspace_doubles_per_ocp();
-cudaError_t solve_prepare();
-// kind 0: load the guess; kind 1: linearise + factorise + export; kind 2: line search / step of SQP iteration it
+// Launch geometry and workspace sizes of one instantiated collocation shape (POLY_ORDER, NUM_SEG)
+struct ShapeInfo {
+    size_t stage_smem, admm_smem;   // dynamic shared memory of the stage kernel / of the (3,6) ADMM kernel (0: none)
+    int stage_threads;
+    size_t ws_doubles;              // per-OCP workspace
+    size_t gmat_doubles;            // per-CTA matrix block in global memory (0: the matrices live in shared memory)
+};
+int shape_supported(int po, int ns);
+cudaError_t shape_info(int po, int ns, ShapeInfo* si);
+cudaError_t solve_prepare(int po, int ns);
+// kind 0: load the guess; kind 1: linearise + factorise + export; kind 2: line search / step of SQP iteration it;
+// kind 3: linearise + factorise + ADMM in one kernel (shape-generic / adaptive-rho path)
 cudaError_t launch_sqp_stage(const KernelConst& kc, const BatchPtrs& bp, int n, int kind, int it, int grid, int* counter, double* workspace,
-                             long long* prof, cudaStream_t stream);
+                             double* gmat, long long* prof, cudaStream_t stream);
 // per-node rigid-body kernels over the whole batch: Jacobians at the iterate / values at the line-search trial points
-cudaError_t launch_node_jac(int n, double* workspace, cudaStream_t stream);
+cudaError_t launch_node_jac(const KernelConst& kc, int n, double* workspace, cudaStream_t stream);
 cudaError_t launch_node_val(const KernelConst& kc, int n, double* workspace, cudaStream_t stream);
 // prof: 16 cycle counters accumulated by CTA 0 in MPCB_PROFILE builds (may be null)
 cudaError_t launch_admm(const KernelConst& kc, int n, int grid, int* counter, double* workspace, long long* prof, cudaStream_t stream);

@@ -23,7 +23,7 @@ MPCB_DEV void lin_a(Ctx<SH>& c, TS<SH>& ts, int tid) {
     const double p = c.z[SH::IP], tsc = c.cheb->ts, reg = c.st->hess_reg, rho = c.st->qp_rho;
     if (tid == 0) { c.scal[SC_PBAR] = p; c.scal[SC_MTP] = -tsc * p; }
     // inequality rows: values + Jacobians were evaluated by node_jac_kernel (mpcb_node.h), one thread per node of the batch
-    for (int e = tid; e < SH::NN * 176; e += NT) c.Jg[e] = c.gJg[e];
+    for (int e = tid; e < SH::NN * 176; e += SH::NT) c.Jg[e] = c.gJg[e];
     if (tid < SH::NINEQ) c.w[SH::NEQ + tid] = c.gGj[tid];
     // collocation rows:  sum_l D[j,l] x_{3s+l} - ts p f = 0   (robot_ocp.hpp:64-70 for f)
     if (tid < SH::NEQ) {
@@ -61,10 +61,10 @@ MPCB_DEV void lin_b(Ctx<SH>& c, TS<SH>& ts, int tid) {
         ts.rho = row_rho(ts.l, ts.u, c.st->qp_rho);
         c.xt[tid] = ts.rho;
     }
-    if (tid >= NT - 32) {
+    if (tid >= SH::NT - 32) {
         double s = 0;
-        for (int i = tid - (NT - 32); i < SH::NVAR - 1; i += 32) s += fabs(c.Ha[i]);
-        c.psum[tid - (NT - 32)] = s;
+        for (int i = tid - (SH::NT - 32); i < SH::NVAR - 1; i += 32) s += fabs(c.Ha[i]);
+        c.psum[tid - (SH::NT - 32)] = s;
     }
 }
 template <class SH>
@@ -90,7 +90,7 @@ MPCB_DEV double* aug_ptr(const Ctx<SH>& c, int s, int m, int nb, int i, int j) {
 
 template <class SH>
 MPCB_DEV void fac_zero(Ctx<SH>& c, int tid) {
-    for (int e = tid; e < SH::MATSIZE + SH::BBSIZE; e += NT) c.W[e] = 0.0;
+    for (int e = tid; e < SH::MATSIZE + SH::BBSIZE; e += SH::NT) c.W[e] = 0.0;
 }
 template <class SH>
 MPCB_DEV void fac_diag(Ctx<SH>& c, TS<SH>& ts, int tid) {
@@ -107,7 +107,7 @@ MPCB_DEV void fac_diag(Ctx<SH>& c, TS<SH>& ts, int tid) {
 // one collocation row (node s*PO+j, component cc) of every segment: S += rho a a^T
 template <class SH>
 MPCB_DEV void fac_eq_row(Ctx<SH>& c, int tid, int j, int cc) {
-    constexpr int GS = NT / SH::NS, NV = SH::PO + 3, NP = NV * (NV + 1) / 2;
+    constexpr int GS = SH::NT / SH::NS, NV = SH::PO + 3, NP = NV * (NV + 1) / 2;
     const int s = tid / GS, lane = tid % GS;
     if (s >= SH::NS || lane >= NP) return;
     const int k = s * SH::PO + j, r = 14 * k + cc, m = SH::m(s), nb = SH::nb(s);
@@ -128,7 +128,7 @@ MPCB_DEV void fac_eq_row(Ctx<SH>& c, int tid, int j, int cc) {
 // the 8 inequality rows of one node of every segment
 template <class SH>
 MPCB_DEV void fac_ineq_node(Ctx<SH>& c, int tid, int jn) {
-    constexpr int GS = NT / SH::NS;
+    constexpr int GS = SH::NT / SH::NS;
     const int s = tid / GS, lane = tid % GS;
     if (s >= SH::NS) return;
     if (jn == SH::PO && s != SH::NS - 1) return;
@@ -152,10 +152,11 @@ MPCB_DEV void fac_ineq_node(Ctx<SH>& c, int tid, int jn) {
 // triangle (diagonal tiles are kept full); one thread keeps one tile in registers for all m pivots.  Per pivot the threads
 // that hold the pivot column publish it (and 1/pivot) in shared memory, one barrier, and every thread applies
 //     a_ij -= a_ik a_kj / a_kk  (i, j != k) ;  a_ik = a_ik / a_kk ;  a_kk = -1 / a_kk
-// to its tile: 25 FMAs against 10 shared-memory loads, no index arithmetic in the inner loop.  Three segments are swept at a
-// time (170 threads each); the separator Schur complement C (kind == NS) goes through the same code afterwards.
+// to its tile: 25 FMAs against 10 shared-memory loads, no index arithmetic in the inner loop.  Sweep<SH>::PAR segments are swept
+// at a time (three for the base shape, 153 threads each); the separator Schur complement C (kind == NS) goes through the same
+// code afterwards.
 // Result: W = -S_II^-1, F = S_II^-1 S_IB, S_BB - S_BI S_II^-1 S_IB  (resp. -C^-1), written back in place.
-constexpr int TILE = 5, SWEEP_SLOT = 170, SWEEP_COLS = 88;
+constexpr int TILE = 5;
 
 template <class SH>
 MPCB_DEV int sweep_m(int kind) { return kind < SH::NS ? SH::m(kind) : SH::NB; }            // number of pivots
@@ -166,13 +167,13 @@ MPCB_DEV double* sweep_ptr(const Ctx<SH>& c, int kind, int i, int j) {     // en
     if (kind < SH::NS) return aug_ptr(c, kind, SH::m(kind), SH::nb(kind), i, j);
     return c.C + i * (i + 1) / 2 + j;
 }
-// which matrix (or -1) and which tile a thread works on in a round; kinds first..first+count-1 share the CTA
+// which matrix (or -1) and which tile a thread works on in a round; kinds first..first+count-1 share the CTA, `slot` threads each
 template <class SH>
-MPCB_DEV void sweep_assign(TS<SH>& ts, int tid, int first, int count) {
-    const int slot = tid / SWEEP_SLOT, t = tid - slot * SWEEP_SLOT;
+MPCB_DEV void sweep_assign(TS<SH>& ts, int tid, int first, int count, int slot) {
+    const int sl = tid / slot, t = tid - sl * slot;
     ts.tseg = -1; ts.tI = 0; ts.tJ = 0;
-    if (slot >= count) return;
-    const int kind = first + slot, nt = (sweep_M<SH>(kind) + TILE - 1) / TILE;
+    if (sl >= count) return;
+    const int kind = first + sl, nt = (sweep_M<SH>(kind) + TILE - 1) / TILE;
     if (t >= nt * (nt + 1) / 2) return;
     int I = 0;
     while ((I + 1) * (I + 2) / 2 <= t) I++;
@@ -180,7 +181,7 @@ MPCB_DEV void sweep_assign(TS<SH>& ts, int tid, int first, int count) {
 }
 template <class SH>
 MPCB_DEV double* sweep_col(const Ctx<SH>& c, int kind, int first, int buf) {
-    return c.colbuf + (buf * 3 + (kind - first)) * SWEEP_COLS;
+    return c.colbuf + (buf * Sweep<SH>::PAR + (kind - first)) * Sweep<SH>::COLS;
 }
 // publish column kn of the thread's matrix (entries it holds) into buffer buf; rn = kn - 5 * (kn / 5) is static
 template <class SH, int RN>
@@ -192,15 +193,15 @@ MPCB_DEV void sweep_publish(const Ctx<SH>& c, const TS<SH>& ts, int first, int k
     if (ts.tJ == Pn) {
         MPCB_UNROLL
         for (int x = 0; x < TILE; x++) col[TILE * ts.tI + x] = ts.tile[TILE * x + RN];
-        if (ts.tI == Pn) col[SWEEP_COLS - 1] = 1.0 / ts.tile[TILE * RN + RN];
+        if (ts.tI == Pn) col[Sweep<SH>::COLS - 1] = 1.0 / ts.tile[TILE * RN + RN];
     } else if (ts.tI == Pn) {
         MPCB_UNROLL
         for (int y = 0; y < TILE; y++) col[TILE * ts.tJ + y] = ts.tile[TILE * RN + y];
     }
 }
 template <class SH>
-MPCB_DEV void sweep_load(const Ctx<SH>& c, TS<SH>& ts, int tid, int first, int count) {
-    sweep_assign(ts, tid, first, count);
+MPCB_DEV void sweep_load(const Ctx<SH>& c, TS<SH>& ts, int tid, int first, int count, int slot) {
+    sweep_assign(ts, tid, first, count, slot);
     const int kind = ts.tseg;
     if (kind < 0) return;
     const int M = sweep_M<SH>(kind);
@@ -220,7 +221,7 @@ MPCB_DEV void sweep_step(const Ctx<SH>& c, TS<SH>& ts, int first, int P) {
     const int kind = ts.tseg, kp = TILE * P + R;
     if (kind < 0 || kp >= sweep_m<SH>(kind)) return;
     const double* col = sweep_col(c, kind, first, kp & 1);
-    const double dinv = col[SWEEP_COLS - 1];
+    const double dinv = col[Sweep<SH>::COLS - 1];
     double ci[TILE], cj[TILE];
     MPCB_UNROLL
     for (int x = 0; x < TILE; x++) { ci[x] = col[TILE * ts.tI + x] * dinv; cj[x] = col[TILE * ts.tJ + x]; }
@@ -252,12 +253,12 @@ MPCB_DEV void sweep_store(const Ctx<SH>& c, const TS<SH>& ts) {
             if (i < M && j <= i) *sweep_ptr(c, kind, i, j) = ts.tile[TILE * x + y];
         }
 }
-// sweep matrices first .. first+count-1 (count <= 3) over all their pivots
+// sweep matrices first .. first+count-1 (count <= Sweep::PAR, `slot` threads each) over all their pivots
 template <class SH>
-MPCB_DEV void sweep_round(MPCB_DRIVER_PARAMS(SH), int first, int count) {
+MPCB_DEV void sweep_round(MPCB_DRIVER_PARAMS(SH), int first, int count, int slot) {
     int mmax = 0;
     for (int k = first; k < first + count; k++) mmax = sweep_m<SH>(k) > mmax ? sweep_m<SH>(k) : mmax;
-    MPCB_PHASE(sweep_load(c, ts, tid, first, count));
+    MPCB_PHASE(sweep_load(c, ts, tid, first, count, slot));
     for (int P = 0; TILE * P < mmax; P++) {
         MPCB_PHASE(sweep_step<SH, 0>(c, ts, first, P));
         MPCB_PHASE(sweep_step<SH, 1>(c, ts, first, P));
@@ -278,7 +279,7 @@ MPCB_DEV int sep_local(int s, int b) {
 }
 template <class SH>
 MPCB_DEV void fac_c_assemble(Ctx<SH>& c, int tid) {
-    for (int e = tid; e < SH::NB * SH::NB; e += NT) {
+    for (int e = tid; e < SH::NB * SH::NB; e += SH::NT) {
         const int i = e / SH::NB, j = e % SH::NB;
         if (j > i) continue;
         double v = (i == j) ? c.rhs[SH::NI + i] : 0.0;
@@ -294,8 +295,6 @@ MPCB_DEV void fac_c_assemble(Ctx<SH>& c, int tid) {
 }
 template <class SH>
 MPCB_DEV void factorise(MPCB_DRIVER_PARAMS(SH)) {
-    static_assert(SH::AUGMAX <= 5 * 17 + 14 && SH::NB <= 85 && 3 * SWEEP_SLOT <= NT && 6 * SWEEP_COLS <= (SH::NS > 1 ? SH::NS : 1) * Layout<SH>::COLSTRIDE,
-                  "sweep tiling: at most 17 x 17 tiles per matrix (170 threads), 3 matrices per round, 6 published columns in colbuf");
     MPCB_PROF_DECL
     MPCB_PHASE(fac_zero(c, tid));
     MPCB_PHASE(fac_diag(c, ts, tid));
@@ -303,10 +302,11 @@ MPCB_DEV void factorise(MPCB_DRIVER_PARAMS(SH)) {
         for (int cc = 0; cc < 14; cc++) MPCB_PHASE(fac_eq_row(c, tid, j, cc));
     for (int jn = 0; jn <= SH::PO; jn++) MPCB_PHASE(fac_ineq_node(c, tid, jn));
     MPCB_PROF(18)
-    for (int first = 0; first < SH::NS; first += 3) sweep_round<SH>(MPCB_DRIVER_ARGS, first, SH::NS - first < 3 ? SH::NS - first : 3);
+    constexpr int PAR = Sweep<SH>::PAR;
+    for (int first = 0; first < SH::NS; first += PAR) sweep_round<SH>(MPCB_DRIVER_ARGS, first, SH::NS - first < PAR ? SH::NS - first : PAR, Sweep<SH>::SLOT_I);
     MPCB_PROF(19)
     MPCB_PHASE(fac_c_assemble(c, tid));
-    sweep_round<SH>(MPCB_DRIVER_ARGS, SH::NS, 1);
+    sweep_round<SH>(MPCB_DRIVER_ARGS, SH::NS, 1, Sweep<SH>::SLOT_C);
     MPCB_PROF(20)
     // W now holds -S_II^-1 (packed lower, per segment), F = S_II^-1 S_IB, C = -(Schur complement)^-1
 }

@@ -34,6 +34,9 @@ struct Shape {
     static constexpr int MMAX = MB + 21 + (NS == 1 ? 14 : 0);
     static constexpr int AUGMAX = MMAX + (NS > 2 ? NBM : NB0);
     static constexpr int VP = ((NA > NVAR ? NA : NVAR) + 7) / 8 * 8;   // padded vector length
+    // threads per CTA of the SQP-stage kernels: thread r owns constraint row r and thread i owns variable i, so NT >= max(NA, NVAR)
+    static constexpr int NT = (NA > 512 || NVAR > 512) ? 1024 : 512;
+    static_assert(NA <= 1024 && NVAR <= 1024, "one thread per constraint row / variable: at most 1024 of each");
 
 #if defined(__CUDACC__)
     __host__ __device__

@@ -5,6 +5,7 @@
 // and the guess/solution plumbing of MotionPlanner::warm_start_RK / solve_trajectory (motionPlanner.cpp:156-207).
 #pragma once
 #include "mpcb_export.h"
+#include "mpcb_gadmm.h"
 #include "mpcb_node.h"
 
 namespace mpcb {
@@ -81,11 +82,11 @@ MPCB_DEV void vio_c(Ctx<SH>& c, int tid) {
     if (tid < SH::NA) e = c.rhs[tid];
     if (tid < SH::NVAR) e = dmax(e, c.xt[tid]);
     umax_accum(c.umax + UM_V, e);
-    if (tid >= NT - 32) {
+    if (tid >= SH::NT - 32) {
         double s = 0;
-        for (int r = tid - (NT - 32); r < SH::NA; r += 32) s += c.rhs[r];
-        for (int i = tid - (NT - 32); i < SH::NVAR; i += 32) s += c.xt[i];
-        c.psum[tid - (NT - 32)] = s;
+        for (int r = tid - (SH::NT - 32); r < SH::NA; r += 32) s += c.rhs[r];
+        for (int i = tid - (SH::NT - 32); i < SH::NVAR; i += 32) s += c.xt[i];
+        c.psum[tid - (SH::NT - 32)] = s;
     }
 }
 template <class SH>
@@ -115,14 +116,14 @@ MPCB_DEV void linearise(MPCB_DRIVER_PARAMS(SH)) {
 template <class SH>
 MPCB_DEV void sqp_mu(Ctx<SH>& c, int tid) {
     double m = 0;
-    for (int i = tid; i < SH::NDUAL; i += NT) m = dmax(m, fabs(c.qp_lam[i]));
+    for (int i = tid; i < SH::NDUAL; i += SH::NT) m = dmax(m, fabs(c.qp_lam[i]));
     umax_accum(c.umax + UM_B, m);
 }
 template <class SH>
 MPCB_DEV void sqp_step(Ctx<SH>& c, int tid, double alpha) {
     double pn = 0, dn = 0;
     if (tid < SH::NVAR) { const double p = c.qp_p[tid]; c.z[tid] += alpha * p; pn = fabs(p); }
-    for (int i = tid; i < SH::NDUAL; i += NT) {
+    for (int i = tid; i < SH::NDUAL; i += SH::NT) {
         const double d = c.qp_lam[i] - c.lam[i];
         c.lam[i] += alpha * d;
         dn = dmax(dn, fabs(d));
@@ -171,6 +172,17 @@ MPCB_DEV void stage_linfac(MPCB_DRIVER_PARAMS(SH), const Problem& pb, double* qb
     MPCB_PROF(25)
     export_qp<SH>(MPCB_DRIVER_ARGS, qb);
     MPCB_PROF(21)
+}
+
+// shape-generic / adaptive-rho variant of stage_linfac: the QP is solved in the same kernel (mpcb_gadmm.h), the result goes to
+// the OCP's result block
+template <class SH>
+MPCB_DEV void stage_qp_generic(MPCB_DRIVER_PARAMS(SH), const Problem& pb, double* qb) {
+    MPCB_PROF_DECL
+    MPCB_PHASE(sqp_load_a(c, tid, pb));
+    linearise<SH>(MPCB_DRIVER_ARGS);
+    MPCB_PROF(17)
+    solve_qp_generic<SH>(MPCB_DRIVER_ARGS, qb + QBL<SH>::G_RES);
 }
 
 template <class SH>

@@ -5,6 +5,7 @@
 #define MPCB_EMUL 1
 #include <vector>
 #include <cstring>
+#include <type_traits>
 #include "mpcb_sqp.h"
 #include "mpcb_host_util.h"
 
@@ -13,27 +14,33 @@ typedef Shape<3, 6> SH36;
 
 template <class SH>
 struct Emu {
-    std::vector<double> smem, z, lam, qb, asmem, jg, gj, gval;
+    std::vector<double> smem, gmat, z, lam, qb, asmem, jg, gj, gval;
     std::vector<TS<SH>> tsv;
-    std::vector<ATS<SH>> atsv;
+    static constexpr bool FAST = SH::PO == 3 && SH::NS == 6;       // the (3,6) ADMM kernel exists for this shape
+    typedef typename std::conditional<FAST, SH, SH36>::type ASH;
+    std::vector<ATS<ASH>> atsv;
     Ctx<SH> c;
-    ACtx<SH> ac;
+    ACtx<ASH> ac;
     ChebConst cheb;
     double limtab[40];
     int flags[2];
     Emu(const mpcb_settings* st, const mpcb_limits* lim)
-        : smem(Layout<SH>::TOTAL, 0.0), z(SH::VP, 0.0), lam(SH::NDUAL + 8, 0.0), qb(AL<SH>::QPBLOCK, 0.0), asmem(AL<SH>::TOTAL, 0.0), jg(SH::NN * 176, 0.0), gj(SH::NINEQ, 0.0),
-          gval(16 * SH::NINEQ, 0.0), tsv(NT), atsv(NT) {
+        : smem(Layout<SH>::TOTAL, 0.0), gmat(Layout<SH>::MATDOUBLES, 0.0), z(SH::VP, 0.0), lam(SH::NDUAL + 8, 0.0), qb(QBL<SH>::QPBLOCK, 0.0), jg(SH::NN * 176, 0.0),
+          gj(SH::NINEQ, 0.0), gval(16 * SH::NINEQ, 0.0), tsv(SH::NT) {
         mpcb_fill_cheb(SH::PO, SH::NS, &cheb);
         fill_limtab(lim, limtab);
-        c.bind(smem.data());
+        c.bind(smem.data(), gmat.data());
         c.z = z.data(); c.lam = lam.data(); c.st = st; c.cheb = &cheb;
         c.gJg = jg.data(); c.gGj = gj.data(); c.gval = gval.data(); c.prof = nullptr;
-        ac.bind(asmem.data());
-        ac.st = st; ac.g = qb.data();
-        std::memset(tsv.data(), 0, sizeof(TS<SH>) * NT);
-        std::memset(atsv.data(), 0, sizeof(ATS<SH>) * NT);
-        for (int tid = 0; tid < NT; tid++) setup_roles(c, tsv[tid], tid);
+        if constexpr (FAST) {
+            asmem.assign(AL<SH>::TOTAL, 0.0);
+            atsv.resize(NT);
+            ac.bind(asmem.data());
+            ac.st = st; ac.g = qb.data();
+            std::memset(atsv.data(), 0, sizeof(ATS<SH>) * NT);
+        }
+        std::memset(tsv.data(), 0, sizeof(TS<SH>) * SH::NT);
+        for (int tid = 0; tid < SH::NT; tid++) setup_roles(c, tsv[tid], tid);
         flags[0] = flags[1] = 0;
     }
     // host stand-ins of node_jac_kernel / node_val_kernel (one "thread" per node / per (trial, node))
@@ -45,21 +52,15 @@ struct Emu {
         const int ntrial = c.st->line_search_max_iter + 1;
         for (int t = 0; t < ntrial; t++)
             for (int k = 0; k < SH::NN; k++)
-                node_val<SH>(z.data(), qb.data() + AL<SH>::G_RES, t, c.st->sqp_tau, k, gval.data() + (t * SH::NN + k) * 8);
+                node_val<SH>(z.data(), qb.data() + QBL<SH>::G_RES, t, c.st->sqp_tau, k, gval.data() + (t * SH::NN + k) * 8);
     }
 };
 
-extern "C" {
-
-int emul_smem_bytes() { return (int)Layout<SH36>::BYTES; }
-int emul_admm_smem_bytes() { return (int)AL<SH36>::BYTES; }
-
-int emul_solve(const mpcb_settings* st, const mpcb_limits* lim, int n, const double* x0, const double* xT, const double* gx,
-               const double* gu, const double* gT, const double* glam, double* sx, double* su, double* sT, double* slam,
-               mpcb_stats* stats) {
-    typedef SH36 SH;
-    const char* why;
-    if (!settings_supported(st, &why)) return MPCB_ERR_UNSUPPORTED;
+template <class SH>
+static int emul_solve_shape(const mpcb_settings* st, const mpcb_limits* lim, int n, const double* x0, const double* xT, const double* gx,
+                            const double* gu, const double* gT, const double* glam, double* sx, double* su, double* sT, double* slam,
+                            mpcb_stats* stats) {
+    const bool generic = settings_generic_path(st) != 0;
     Emu<SH> e(st, lim);
     for (int i = 0; i < n; i++) {
         Problem pb;
@@ -74,13 +75,35 @@ int emul_solve(const mpcb_settings* st, const mpcb_limits* lim, int n, const dou
         for (int it = 1; it <= st->sqp_max_iter; it++) {
             if (e.flags[0]) break;
             e.node_jac_all();
-            stage_linfac<SH>(e.c, e.tsv.data(), pb, e.qb.data());
-            admm_run<SH>(e.ac, e.atsv.data());
+            if (generic) stage_qp_generic<SH>(e.c, e.tsv.data(), pb, e.qb.data());
+            else if constexpr (SH::PO == 3 && SH::NS == 6) {
+                stage_linfac<SH>(e.c, e.tsv.data(), pb, e.qb.data());
+                admm_run<SH>(e.ac, e.atsv.data());
+            }
             e.node_val_all();
             stage_lsstep<SH>(e.c, e.tsv.data(), pb, e.qb.data(), e.flags, it);
         }
     }
     return 0;
+}
+
+extern "C" {
+
+int emul_smem_bytes() { return (int)Layout<SH36>::BYTES; }
+int emul_admm_smem_bytes() { return (int)AL<SH36>::BYTES; }
+
+int emul_solve(const mpcb_settings* st, const mpcb_limits* lim, int n, const double* x0, const double* xT, const double* gx,
+               const double* gu, const double* gT, const double* glam, double* sx, double* su, double* sT, double* slam,
+               mpcb_stats* stats) {
+    const char* why;
+    if (!settings_supported(st, &why)) return MPCB_ERR_UNSUPPORTED;
+#define EMUL_ARGS st, lim, n, x0, xT, gx, gu, gT, glam, sx, su, sT, slam, stats
+    if (st->poly_order == 3 && st->num_seg == 6) return emul_solve_shape<Shape<3, 6>>(EMUL_ARGS);
+    if (st->poly_order == 3 && st->num_seg == 12) return emul_solve_shape<Shape<3, 12>>(EMUL_ARGS);
+    if (st->poly_order == 5 && st->num_seg == 6) return emul_solve_shape<Shape<5, 6>>(EMUL_ARGS);
+    if (st->poly_order == 7 && st->num_seg == 4) return emul_solve_shape<Shape<7, 4>>(EMUL_ARGS);
+#undef EMUL_ARGS
+    return MPCB_ERR_UNSUPPORTED;
 }
 
 // Debug entry: linearise at (z, lam) given in polympc order, factorise, export, and apply S^-1 to `rhs` (polympc order)

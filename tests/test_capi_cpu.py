@@ -44,14 +44,17 @@ def test_no_cpu_fallback():
 def test_unsupported_settings_fail_loudly():
     L = M.load_library()
     h = C.c_void_p()
-    for kw in (dict(qp_adaptive_rho=1), dict(poly_order=5), dict(num_seg=12)):
+    for kw in (dict(poly_order=4), dict(num_seg=5), dict(poly_order=5, num_seg=12), dict(qp_adaptive_rho=1, qp_adaptive_rho_tolerance=1.0),
+               dict(line_search_max_iter=16)):
         rc = L.mpcb_create(C.byref(M.default_settings(**kw)), 0, C.byref(h))
         assert rc == -3 and not h.value
         assert L.mpcb_last_error(None)
 
 
-def test_time_nodes_match_oracle(oracle):
-    assert np.array_equal(M.time_nodes(M.default_settings()), oracle.time_nodes(oracle.default_settings()))
+@pytest.mark.parametrize("po,ns", [(3, 6), (3, 12), (5, 6), (7, 4)])
+def test_time_nodes_match_oracle(oracle, po, ns):
+    t = M.time_nodes(M.default_settings(poly_order=po, num_seg=ns))
+    assert len(t) == po * ns + 1 and np.abs(t - oracle.time_nodes(oracle.default_settings(poly_order=po, num_seg=ns))).max() < 1e-15
 
 
 def test_generator_is_deterministic_and_in_bounds(oracle):
@@ -120,3 +123,17 @@ def test_tool_pose_and_inverse_kinematic():
             assert np.abs(R2 - R).max() < 2e-4 and np.abs(p2 - p).max() < 2e-4
             converged += 1
     assert converged >= 6
+
+
+def test_no_miscompiled_shared_base():
+    """ptxas 12.9 once rematerialised the dynamic shared-memory base of the 1024-thread stage kernels as `ULEA URa, URb, URb, 0x18`
+    (both operands the same register: CTA-rank bits taken from the base itself), which faults on the device with 'illegal memory
+    access' (found in round 2, csrc/mpcb_kernels.cu sqp_stage_kernel).  The shipped SASS must not contain that pattern."""
+    import re
+    import shutil
+    import subprocess
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    sass = subprocess.run(["cuobjdump", "-sass", M.capi.lib_path()], capture_output=True, text=True, check=True).stdout
+    assert "sqp_stage_kernel" in sass and "admm_kernel" in sass
+    assert not re.search(r"ULEA UR(\d+), UR(\d+), UR\2, 0x18", sass)

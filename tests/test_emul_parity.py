@@ -68,3 +68,24 @@ def test_emulated_kernel_warm_started_duals(setup):
     o2 = O.solve(s, lim, x0[0], xT[0], sx[0], su[0], sT[0], glam=slam[0], want_lam=True)
     assert abs(o2[2] - e2[2][0]) <= 1e-6 * abs(o2[2])
     assert np.abs(o2[0] - e2[0][0]).max() < 1e-5 and np.abs(o2[1] - e2[1][0]).max() < 1e-5
+
+
+@pytest.mark.parametrize("po,ns,adaptive", [(3, 12, 0), (5, 6, 0), (7, 4, 0), (3, 6, 1)])
+def test_emulated_generic_path_matches_oracle(oracle, po, ns, adaptive):
+    """BASELINE config 4 (other collocation shapes, robot_ocp.hpp:31-42) and adaptive rho: the shape-generic stage (mpcb_gadmm.h,
+    factorise + ADMM in one kernel) in the lockstep emulation against the oracle."""
+    O = oracle
+    m = [0.8, 0.8, 0.6, 0.9, 0.1]
+    s = O.default_settings(poly_order=po, num_seg=ns, qp_adaptive_rho=adaptive)
+    lim = O.default_limits(m)
+    ms = M.default_settings(poly_order=po, num_seg=ns)
+    x0, xT = M.generate_problems(M.default_limits(m), 0, 1, 2)
+    gx, gu, gT = M.guess_batch(ms, M.default_limits(m), x0, xT)
+    esx, esu, eT, elam, est = E.solve(s, lim, x0, xT, gx, gu, gT, want_lam=True)
+    for i in range(2):
+        osx, osu, oT, olam, ost = O.solve(s, lim, x0[i], xT[i], gx[i], gu[i], gT[i], want_lam=True)
+        assert abs(oT - eT[i]) <= 1e-6 * abs(oT)
+        assert np.abs(osx - esx[i]).max() < 1e-5 and np.abs(osu - esu[i]).max() < 1e-5
+        assert np.abs(olam - elam[i]).max() < 1e-5 * max(1.0, np.abs(olam).max())
+        assert (ost.status, ost.sqp_iters, list(ost.qp_iters), list(ost.qp_status), list(ost.ls_trials), list(ost.alpha)) == \
+               (est[i].status, est[i].sqp_iters, list(est[i].qp_iters), list(est[i].qp_status), list(est[i].ls_trials), list(est[i].alpha))

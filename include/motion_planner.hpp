@@ -65,8 +65,12 @@ class PandaWrapper {
     double max_torqueDot = 1000;
     double max_linear_velocity = 1.7, max_angular_velocity = 2.5;      // pandaWrapper.hpp:37-38
     double min_height = 0.05;                                          // pandaWrapper.hpp:40
-    explicit PandaWrapper(const std::string& /*urdf_path*/) {
-        // the model is baked from robot_utils/panda-model/panda_arm.urdf at build time (tools/bake_panda_model.py)
+    explicit PandaWrapper(const std::string& urdf_path) {
+        // the model is baked from robot_utils/panda-model/panda_arm.urdf at build time (tools/bake_panda_model.py): any other
+        // model file is refused instead of being ignored
+        const std::string::size_type slash = urdf_path.find_last_of("/\\");
+        const std::string base = slash == std::string::npos ? urdf_path : urdf_path.substr(slash + 1);
+        if (base != "panda_arm.urdf") throw std::invalid_argument("PandaWrapper: only panda_arm.urdf is supported (the model is baked at build time), got '" + urdf_path + "'");
         mpcb_limits l;
         mpcb_default_limits(&l);
         for (int j = 0; j < 7; j++) {
@@ -131,11 +135,15 @@ class MotionPlanner {
     MotionPlanner& operator=(const MotionPlanner&) = delete;
 
     // motionPlanner.cpp:27-39: final state box = target +- eps
-    void set_target_state(const Vec7& q, const Vec7& v, const Vec7& /*a*/ = Vec7::Zero()) {
+    // The acceleration argument only feeds Ruckig in the reference (motionPlanner.cpp:36-38); the profile generator here starts and
+    // ends at rest in acceleration, so a nonzero value is refused instead of being dropped silently.
+    void set_target_state(const Vec7& q, const Vec7& v, const Vec7& a = Vec7::Zero()) {
+        require_zero_acceleration(a, "set_target_state");
         for (int j = 0; j < 7; j++) { target_state[j] = q[j]; target_state[7 + j] = v[j]; }
     }
     // motionPlanner.cpp:41-54: initial state pinned
-    void set_current_state(const Vec7& q, const Vec7& v, const Vec7& /*a*/ = Vec7::Zero()) {
+    void set_current_state(const Vec7& q, const Vec7& v, const Vec7& a = Vec7::Zero()) {
+        require_zero_acceleration(a, "set_current_state");
         for (int j = 0; j < 7; j++) { current_state[j] = q[j]; current_state[7 + j] = v[j]; }
     }
     // motionPlanner.cpp:56-90
@@ -143,11 +151,14 @@ class MotionPlanner {
         margin_position_ = mp; margin_velocity_ = mv; margin_acceleration_ = ma; margin_torque_ = mt; margin_jerk_ = mj;
         limits_.margins[0] = mp; limits_.margins[1] = mv; limits_.margins[2] = ma; limits_.margins[3] = mt; limits_.margins[4] = mj;
         limits_.min_height = robot.min_height;
-        mpcb_set_limits(h_, &limits_);
+        push_limits();
     }
-    void set_min_height(double min_height) { limits_.min_height = min_height; mpcb_set_limits(h_, &limits_); }    // motionPlanner.cpp:92-100
+    void set_min_height(double min_height) { limits_.min_height = min_height; push_limits(); }    // motionPlanner.cpp:92-100
     // motionPlanner.cpp:102-114 (rejection on the height of joint 7)
-    void sample_random_state(Vec7& q, Vec7& v) { mpcb_sample_random_state(&limits_, seed_, stream_++, q.data(), v.data()); }
+    void sample_random_state(Vec7& q, Vec7& v) {
+        if (mpcb_sample_random_state(&limits_, seed_, stream_++, q.data(), v.data()) != MPCB_OK)
+            throw std::runtime_error("MotionPlanner::sample_random_state: min_height is out of the robot's reach");
+    }
     // motionPlanner.cpp:116-144: 0 ok, 1 position, 2 velocity, 3 both, +10 acceleration
     int check_state_in_bounds(const Vec7& q, const Vec7& v, const Vec7& a = Vec7::Zero()) const {
         bool pc = false, vc = false, ac = false;
@@ -287,6 +298,14 @@ class MotionPlanner {
         }
     }
 
+    void push_limits() {
+        const int rc = mpcb_set_limits(h_, &limits_);
+        if (rc != MPCB_OK) throw std::runtime_error(std::string("MotionPlanner: mpcb_set_limits failed: ") + mpcb_last_error(h_));
+    }
+    static void require_zero_acceleration(const Vec7& a, const char* who) {
+        for (int j = 0; j < 7; j++)
+            if (a[j] != 0.0) throw std::invalid_argument(std::string("MotionPlanner::") + who + ": nonzero boundary accelerations are not supported by the profile generator");
+    }
     mpcb_handle* h_ = nullptr;
     mpcb_settings settings_;
     mpcb_limits limits_;
@@ -295,7 +314,7 @@ class MotionPlanner {
     double p_guess_ = 1.0, sol_T_ = 0.0, rk_T_ = 1.0;
     mpcb_otg_traj rk_traj_{};
     bool rk_ok_ = false;
-    State rk_x0_, rk_xT_;
+    State rk_x0_{}, rk_xT_{};
     bool carry_duals_ = false;
     unsigned long long seed_ = 0, stream_ = 0;
 };

@@ -24,7 +24,7 @@ typedef enum {
     MPCB_OK = 0,
     MPCB_ERR_NO_DEVICE = -1,     /* no CUDA device / driver: the product has no CPU path */
     MPCB_ERR_BAD_ARG = -2,
-    MPCB_ERR_UNSUPPORTED = -3,   /* (poly_order, num_seg) not instantiated, or an option the kernels do not implement */
+    MPCB_ERR_UNSUPPORTED = -3,   /* (poly_order, num_seg) not one of the instantiated shapes (3,6), (3,12), (5,6), (7,4), or a setting out of range */
     MPCB_ERR_CUDA = -4,          /* a CUDA runtime call failed; see mpcb_last_error() */
     MPCB_ERR_ALLOC = -5
 } mpcb_error;
@@ -38,7 +38,8 @@ typedef struct {
     int qp_max_iter;              /* motionPlanner.cpp:16 (700) */
     int line_search_max_iter;     /* motionPlanner.cpp:17 (10 -> at most 9 trials, polympc_redef.hpp:101) */
     int qp_check_termination;     /* boxADMM: residual test every 25 iterations */
-    int qp_adaptive_rho;          /* boxADMM adaptive rho (0 = off; 1 is MPCB_ERR_UNSUPPORTED in this version) */
+    int qp_adaptive_rho;          /* boxADMM adaptive rho: 0 = fixed rho (default); 1 = rho re-estimated at the residual checks every
+                                   * qp_adaptive_rho_interval iterations, KKT re-factorised when it moved by more than the tolerance factor */
     int qp_adaptive_rho_interval;
     double qp_eps_abs;            /* motionPlanner.cpp:20 (1e-3) */
     double qp_eps_rel;            /* motionPlanner.cpp:19 (1e-3) */
@@ -96,7 +97,9 @@ int mpcb_num_dual(const mpcb_settings* s);
 /* Normalised node times in [0,1], ascending (polympc `time_nodes`; motionPlanner.cpp:156). */
 int mpcb_time_nodes(const mpcb_settings* s, double* t /*N*/);
 
-/* One handle per CUDA device; not thread-safe; replaces the `mpc_t mpc` member (motionPlanner.hpp:28-29). */
+/* One handle per CUDA device; not thread-safe; replaces the `mpc_t mpc` member (motionPlanner.hpp:28-29).
+ * A handle owns one workspace: calls that pass different streams are serialised on the device (a call on a new stream first
+ * waits for the handle's previous call), so one handle never has two solves in flight; use one handle per concurrent stream. */
 int mpcb_create(const mpcb_settings* s, int device, mpcb_handle** out);
 void mpcb_destroy(mpcb_handle* h);
 const char* mpcb_last_error(const mpcb_handle* h);   /* h may be NULL: error of the last failed mpcb_create */

@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "mpcb.h"
+#include "mpcb_gen.h"
 #include "mpcb_host_util.h"
 #include "mpcb_kernels.h"
 
@@ -36,6 +37,11 @@ struct mpcb_handle {
     void* d_stage = nullptr;
     size_t stage_bytes = 0;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // one in-flight stream per handle: work enqueued on another stream first waits for the handle's last enqueue (the
+    // workspace, counters and staging buffers are per handle, not per stream)
+    cudaEvent_t ev_last = nullptr;
+    cudaStream_t last_stream = nullptr;
+    bool busy = false;
     bool timed = false;
     cudaStream_t timed_stream = nullptr;
     long long launches = 0;
@@ -98,7 +104,8 @@ int mpcb_create(const mpcb_settings* s, int device, mpcb_handle** out) {
     h->grid_max = h->sm_count;      // one CTA per SM (shared memory bound)
     if (h->si.gmat_doubles && (e = cudaMalloc(&h->d_gmat, sizeof(double) * h->si.gmat_doubles * (size_t)h->grid_max)) != cudaSuccess) return fail("cudaMalloc(matrix blocks)", e);
     if ((e = cudaMalloc(&h->d_prof, 512 * sizeof(long long))) != cudaSuccess || (e = cudaMemset(h->d_prof, 0, 512 * sizeof(long long))) != cudaSuccess) return fail("cudaMalloc(prof)", e);
-    if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess) return fail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&h->ev_last, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
     *out = h;
     return MPCB_OK;
 }
@@ -114,6 +121,7 @@ void mpcb_destroy(mpcb_handle* h) {
     for (cudaEvent_t e : h->kev) cudaEventDestroy(e);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
+    if (h->ev_last) cudaEventDestroy(h->ev_last);
     delete h;
 }
 
@@ -126,8 +134,21 @@ int mpcb_set_limits(mpcb_handle* h, const mpcb_limits* lim) {
     return MPCB_OK;
 }
 
+// serialise the handle's work across streams (see mpcb_handle::ev_last)
+static cudaError_t handle_enter(mpcb_handle* h, cudaStream_t stream) {
+    if (h->busy && h->last_stream != stream) return cudaStreamWaitEvent(stream, h->ev_last, 0);
+    return cudaSuccess;
+}
+static cudaError_t handle_leave(mpcb_handle* h, cudaStream_t stream) {
+    h->busy = true; h->last_stream = stream;
+    return cudaEventRecord(h->ev_last, stream);
+}
+// before a per-handle buffer is freed: everything enqueued so far has finished
+static void handle_quiesce(mpcb_handle* h) { if (h->busy) cudaEventSynchronize(h->ev_last); }
+
 static int ensure_stage(mpcb_handle* h, size_t bytes) {
     if (bytes <= h->stage_bytes) return MPCB_OK;
+    handle_quiesce(h);
     if (h->d_stage) { cudaFree(h->d_stage); h->d_stage = nullptr; h->stage_bytes = 0; }
     cudaError_t e = cudaMalloc(&h->d_stage, bytes);
     if (e != cudaSuccess) { h->err = std::string("cudaMalloc(stage): ") + cudaGetErrorString(e); return MPCB_ERR_ALLOC; }
@@ -140,6 +161,7 @@ static size_t al(size_t b) { return (b + 255) / 256 * 256; }
 static const int CHUNK_MAX = 4096;
 
 static int ensure_workspace(mpcb_handle* h, int ocps, int counters) {
+    if (ocps > h->ws_ocps || counters > h->n_counter) handle_quiesce(h);
     if (ocps > h->ws_ocps) {
         if (h->d_workspace) { cudaFree(h->d_workspace); h->d_workspace = nullptr; h->ws_ocps = 0; }
         cudaError_t e = cudaMalloc(&h->d_workspace, sizeof(double) * h->si.ws_doubles * (size_t)ocps);
@@ -181,6 +203,7 @@ int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, 
     if (n == 0) return MPCB_OK;
     cudaStream_t stream = (cudaStream_t)stream_;
     CK(cudaSetDevice(h->device));
+    CK(handle_enter(h, stream));
     const int N = mpcb_num_nodes(&h->st), ND = mpcb_num_dual(&h->st);
     const size_t bx0 = sizeof(double) * 14 * n, bgx = sizeof(double) * 14 * N * n, bgu = sizeof(double) * 7 * N * n, bT = sizeof(double) * n,
                  blam = sizeof(double) * ND * n, bst = sizeof(mpcb_stats) * n;
@@ -267,6 +290,7 @@ int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, 
         if (stats) CK(cudaMemcpyAsync(stats, bp.stats, bst, cudaMemcpyDeviceToHost, stream));
         CK(cudaStreamSynchronize(stream));
     }
+    CK(handle_leave(h, stream));
     return MPCB_OK;
 }
 
@@ -278,6 +302,7 @@ int mpcb_sample_batch(mpcb_handle* h, int n, const double* sol_x, const double* 
     if (n == 0 || (!traj && !acc)) return MPCB_OK;
     cudaStream_t stream = (cudaStream_t)stream_;
     CK(cudaSetDevice(h->device));
+    CK(handle_enter(h, stream));
     const int N = mpcb_num_nodes(&h->st);
     const size_t bsx = sizeof(double) * 14 * N * n, bsu = sizeof(double) * 7 * N * n, bT = sizeof(double) * n, btg = sizeof(double) * 14 * n,
                  btraj = sizeof(double) * 29 * (npts + 1) * n, bacc = sizeof(mpcb_account) * n;
@@ -310,6 +335,7 @@ int mpcb_sample_batch(mpcb_handle* h, int n, const double* sol_x, const double* 
         if (acc) CK(cudaMemcpyAsync(acc, dacc, bacc, cudaMemcpyDeviceToHost, stream));
         CK(cudaStreamSynchronize(stream));
     }
+    CK(handle_leave(h, stream));
     return MPCB_OK;
 }
 
@@ -320,6 +346,7 @@ int mpcb_guess_batch_gpu(mpcb_handle* h, int n, const double* x0, const double* 
     if (n == 0) return MPCB_OK;
     cudaStream_t stream = (cudaStream_t)stream_;
     CK(cudaSetDevice(h->device));
+    CK(handle_enter(h, stream));
     OtgConst oc;
     oc.N = mpcb_num_nodes(&h->st);
     if (oc.N > 64 || mpcb_time_nodes(&h->st, oc.tn) != MPCB_OK) { h->err = "unsupported number of nodes"; return MPCB_ERR_UNSUPPORTED; }
@@ -350,6 +377,7 @@ int mpcb_guess_batch_gpu(mpcb_handle* h, int n, const double* x0, const double* 
         CK(cudaMemcpyAsync(gT, dgT, bT, cudaMemcpyDeviceToHost, stream));
         CK(cudaStreamSynchronize(stream));
     }
+    CK(handle_leave(h, stream));
     return MPCB_OK;
 }
 
@@ -357,10 +385,12 @@ int mpcb_generate_problems_gpu(mpcb_handle* h, int kind, unsigned long long seed
                                void* stream_) {
     if (!h) return MPCB_ERR_BAD_ARG;
     if (n < 0 || (n > 0 && (!x0 || !xT)) || (kind != 0 && kind != 1)) { h->err = "bad argument"; return MPCB_ERR_BAD_ARG; }
+    if (!(h->lim.min_height <= MPCB_GEN_MAX_HEIGHT)) { h->err = "min_height is out of the robot's reach: the rejection sampler would not terminate"; return MPCB_ERR_BAD_ARG; }
     if (mem != MPCB_MEM_HOST && mem != MPCB_MEM_DEVICE) { h->err = "mem must be MPCB_MEM_HOST or MPCB_MEM_DEVICE"; return MPCB_ERR_BAD_ARG; }
     if (n == 0) return MPCB_OK;
     cudaStream_t stream = (cudaStream_t)stream_;
     CK(cudaSetDevice(h->device));
+    CK(handle_enter(h, stream));
     const size_t b14 = sizeof(double) * 14 * n;
     double *da = x0, *db = xT;
     if (mem == MPCB_MEM_HOST) {
@@ -375,6 +405,7 @@ int mpcb_generate_problems_gpu(mpcb_handle* h, int kind, unsigned long long seed
         CK(cudaMemcpyAsync(xT, db, b14, cudaMemcpyDeviceToHost, stream));
         CK(cudaStreamSynchronize(stream));
     }
+    CK(handle_leave(h, stream));
     return MPCB_OK;
 }
 

@@ -64,6 +64,7 @@ MPCB_HD void inverse_velocities(const double* q, const double* task, double* qd)
     for (int i = 5; i >= 0; i--) { double s = y[i]; for (int k = i + 1; k < 6; k++) s -= L[k * 6 + i] * y[k]; y[i] = s; }
     for (int j = 0; j < 7; j++) { double s = 0; for (int r = 0; r < 6; r++) s += J[r * 7 + j] * y[r]; qd[j] = s; }
 }
+#define MPCB_GEN_MAX_HEIGHT 1.0     /* joint 7 of the Panda reaches about 1.19 m; above 1.0 m the rejection loop hardly ever accepts */
 MPCB_HD double norm3(const double* v) { return sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]); }
 
 // sample_random_state (motionPlanner.cpp:102-114): rejection on the height of JOINT 7 (not the tool, Q12)
@@ -71,6 +72,7 @@ MPCB_HD void sample_random_state(const mpcb_limits* lim, Rng& rng, double* q, do
     const double mp = lim->margins[0], mv = lim->margins[1];
     const double zero[3] = {0, 0, 0};
     double pos[3];
+    int tries = 0;        // capped: an unreachable min_height must not hang a CPU thread or a GPU (the entry points refuse min_height > MPCB_GEN_MAX_HEIGHT)
     do {
         for (int j = 0; j < 7; j++) {
             const double range = lim->qmax[j] - lim->qmin[j];
@@ -78,7 +80,7 @@ MPCB_HD void sample_random_state(const mpcb_limits* lim, Rng& rng, double* q, do
             q[j] = 0.5 * (rng.sym() * (range - 2 * safety) + (lim->qmax[j] + lim->qmin[j]));
         }
         rbd::fk_point7(q, zero, pos);
-    } while (pos[2] < lim->min_height);
+    } while (pos[2] < lim->min_height && ++tries < (1 << 16));
     for (int j = 0; j < 7; j++) v[j] = mv * rng.sym() * lim->vmax[j];
 }
 // Cartesian scale-downs shared by both examples (benchmark.cpp:25-36, offline_trajectory.cpp:26-39)

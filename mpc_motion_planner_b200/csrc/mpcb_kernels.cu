@@ -267,7 +267,7 @@ otg_guess_kernel(const __grid_constant__ OtgConst oc, const int n, const double*
         for (int round = 0; round < MPCB_OTG_ROUNDS && !all; round++) {
             bool good = true;
             double tn = T;
-            need = act && Tmin < T * (1 - 1e-15);
+            need = act && Tmin < T * (1 - 1e-15) && !otg::is_hold(q1 - q0, v0, v1);
             if (need) good = otg::sync_scan(q1 - q0, v0, v1, vl, al, jl, T, vco, &lo, &hi, &tn);
             all = (__ballot_sync(gmask, !good) & gmask) == 0;
             if (all) break;

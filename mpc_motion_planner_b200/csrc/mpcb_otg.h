@@ -52,8 +52,14 @@ MPCB_HD Eval eval_vc(double dp, double v0, double vT, double vc, double amax, do
 
 #define MPCB_OTG_GRID 512
 
+// a joint that does not move at all (same position, at rest at both ends): its profile is "stay", for any duration.  Ruckig
+// accepts such input (moving a subset of the joints is the common case); the cruise-velocity search below cannot represent it
+// (vc = 0 with an arbitrary cruise time), so it is handled apart: Tmin = 0, never synchronised, all phases empty.
+MPCB_HD bool is_hold(double dp, double v0, double vT) { return fabs(dp) <= 1e-12 && fabs(v0) <= 1e-12 && fabs(vT) <= 1e-12; }
+
 // step 1: minimum duration and its cruise velocity
 MPCB_HD bool min_time(double dp, double v0, double vT, double vmax, double amax, double jmax, double* Tmin, double* vcbest) {
+    if (is_hold(dp, v0, vT)) { *Tmin = 0.0; *vcbest = 0.0; return true; }
     double best = INFINITY, bvc = 0;
     for (int s = -1; s <= 1; s += 2) {
         const Eval e = eval_vc(dp, v0, vT, s * vmax, amax, jmax);
@@ -199,7 +205,7 @@ inline int calculate(const mpcb_limits* lim, const double* x0, const double* xT,
         all = true;
         double Tn = T;
         for (int d = 0; d < 7; d++) {
-            need[d] = Tmin[d] < T * (1 - 1e-15);
+            need[d] = Tmin[d] < T * (1 - 1e-15) && !is_hold(xT[d] - x0[d], x0[7 + d], xT[7 + d]);
             if (!need[d]) continue;
             double tn;
             if (!sync_scan(xT[d] - x0[d], x0[7 + d], xT[7 + d], vl[d], al[d], jl[d], T, vco[d], &lo[d], &hi[d], &tn)) { all = false; Tn = fmax(Tn, tn); }
@@ -213,7 +219,7 @@ inline int calculate(const mpcb_limits* lim, const double* x0, const double* xT,
         const double dp = xT[d] - x0[d];
         const double vc = need[d] ? sync_bisect(dp, x0[7 + d], xT[7 + d], al[d], jl[d], T, lo[d], hi[d]) : vco[d];
         const Eval e = eval_vc(dp, x0[7 + d], xT[7 + d], vc, al[d], jl[d]);
-        fill_dof(tr, d, x0[d], x0[7 + d], xT[7 + d], vc, e.tc, al[d], jl[d]);
+        fill_dof(tr, d, x0[d], x0[7 + d], xT[7 + d], vc, is_hold(dp, x0[7 + d], xT[7 + d]) ? T : e.tc, al[d], jl[d]);
     }
     tr->T = T; tr->status = status;
     return status;

@@ -4,9 +4,8 @@
 //                            + the target generation of examples/benchmark.cpp:19-42 (kind 0) and
 //                            examples/offline_trajectory.cpp:18-41 (kind 1), using PandaWrapper::inverse_velocities /
 //                            forward_velocities (robot_utils/pandaWrapper.cpp:60-107).
-//   mpcb_guess_batch       : MotionPlanner::warm_start_RK (motionPlanner.cpp:146-175) on the jerk-limited profiles of mpcb_otg.h; (old note:) Ruckig is not
-//                            available in this environment, so the guess is a time-scaled cubic
-//                            Hermite joint profile sampled at polympc's node times; see DESIGN.md.
+//   mpcb_guess_batch       : MotionPlanner::warm_start_RK (motionPlanner.cpp:146-175) on the jerk-limited profiles of mpcb_otg.h (the role of Ruckig<7>),
+//                            sampled at polympc's node times; inputs the generator rejects get a time-scaled cubic Hermite profile.
 #include <math.h>
 #include <stdint.h>
 #include <string.h>
@@ -30,13 +29,14 @@ extern "C" {
 
 int mpcb_generate_problems(const mpcb_limits* lim, int kind, unsigned long long seed, int n, double* x0, double* xT) {
     if (!lim || !x0 || !xT || n < 0 || (kind != 0 && kind != 1)) return MPCB_ERR_BAD_ARG;
+    if (!(lim->min_height <= MPCB_GEN_MAX_HEIGHT)) return MPCB_ERR_BAD_ARG;      // out of reach: the rejection sampler would not terminate
     for (int i = 0; i < n; i++) generate_one(lim, kind, seed, (uint64_t)i, x0 + 14 * (size_t)i, xT + 14 * (size_t)i);
     return MPCB_OK;
 }
 
 // ---- single-state helpers for the MotionPlanner mirror (include/motion_planner.hpp) -----------------------------------
 int mpcb_sample_random_state(const mpcb_limits* lim, unsigned long long seed, unsigned long long stream, double* q, double* v) {
-    if (!lim || !q || !v) return MPCB_ERR_BAD_ARG;
+    if (!lim || !q || !v || !(lim->min_height <= MPCB_GEN_MAX_HEIGHT)) return MPCB_ERR_BAD_ARG;
     Rng rng(seed, stream);
     sample_random_state(lim, rng, q, v);
     return MPCB_OK;

@@ -21,6 +21,7 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <thread>
@@ -555,7 +556,9 @@ struct QPResult { int status; int iters; double rp, rd, ep, ed; };
 QPResult qp_admm(const Dims& d, const orc_settings* st, const double* zlin, const double* Jg, const double* Hd, const double* Ha,
                  const double* h, const double* lA, const double* uA, const double* lb, const double* ub, double* xout, double* yout) {
     const int n = d.nvar, m = d.na, ip = d.ip();
-    const double RHO_TOL = 1e-4, RHO_EQ = 1e3, RHO_MIN = 1e-6, LOOSE = 1e16;
+    // ORC_EXP_RHO_EQ: experiment knob of tools/calibrate_admm.py only (equality-row penalty factor); default 1e3
+    static const double RHO_EQ = std::getenv("ORC_EXP_RHO_EQ") ? std::atof(std::getenv("ORC_EXP_RHO_EQ")) : 1e3;
+    const double RHO_TOL = 1e-4, RHO_MIN = 1e-6, LOOSE = 1e16;
     double rho = st->qp_rho;
     const double sigma = st->qp_sigma, alpha = st->qp_alpha;
     std::vector<double> rhoA(m), rhoB(n);

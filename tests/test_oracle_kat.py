@@ -97,3 +97,19 @@ def test_chebyshev_nodes_and_D(oracle):
         xi = -np.cos(np.pi * np.arange(po + 1) / po)
         for deg in range(po + 1):
             assert np.allclose(D2 @ xi ** deg, deg * xi ** max(deg - 1, 0) if deg else 0 * xi, atol=1e-10)
+
+
+def test_oracle_embedded_end_to_end_band(oracle):
+    """The reference's only embedded end-to-end result (analysis/data_analysis.ipynb cell 1, '1SQP_700QP'): one SQP iteration of the
+    oracle from the embedded Ruckig samples lands within |dT| <= 0.01 of T = 1.55469 and within 0.05 rad of the recovered node
+    positions -- the band tools/calibrate_admm.py shows the data support (parity with polympc itself stays unpinned)."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import calibrate_admm as Cal
+    emb, t, x0, xT, gx, gu, T = Cal.embedded_problem(oracle)
+    o = oracle.solve(oracle.default_settings(sqp_max_iter=1), oracle.default_limits(Cal.OFFLINE_MARGINS), x0, xT, gx, gu, T)
+    assert abs(o[2] - Cal.T_REF) <= 0.01
+    ref = Cal.reference_nodes(emb, t)
+    assert np.abs(o[0].reshape(19, 14)[:, :7] - ref[:, :7]).max() <= 0.05
+    assert o[4].qp_iters[0] == 700 and o[4].qp_status[0] == 2          # the QP runs into its cap (SURVEY B.4)

@@ -101,3 +101,40 @@ def test_guess_batch_samples_the_profile():
             q, v, a = M.otg_at_time(tr, tk * tr.T)         # motionPlanner.cpp:156-165
             assert np.array_equal(gx[i, 14 * k:14 * k + 7], q) and np.array_equal(gx[i, 14 * k + 7:14 * k + 14], v)
             assert np.array_equal(gu[i, 7 * k:7 * k + 7], a)
+
+
+def test_stationary_joints_are_hold_profiles():
+    """Joints that do not move (same position, at rest at both ends) get a 'stay' profile and do not block the others -- moving
+    a subset of the joints is the common real-world input and Ruckig accepts it (motionPlanner.cpp:146-160)."""
+    m = [0.9, 0.9, 0.5, 0.9, 0.1]
+    lim = M.default_limits(m)
+    s = M.default_settings()
+    x0, xT = M.generate_problems(lim, 1, 11, 1)
+    x0 = x0[0].copy(); xT = xT[0].copy()
+    x0[7:] = 0.0; xT[7:] = 0.0
+    ref_rc, ref = M.otg_calculate(lim, x0, xT)
+    assert ref_rc >= 0
+    for held in ([3], [1, 2, 3, 4, 5, 6], [0, 6]):
+        a = x0.copy(); b = xT.copy()
+        for j in held:
+            b[j] = a[j]
+        rc, tr = M.otg_calculate(lim, a, b)
+        assert rc >= 0, (held, rc)
+        moving = [j for j in range(7) if j not in held]
+        assert tr.T > 0
+        for t in np.linspace(0.0, tr.T, 23):
+            q, v, acc = M.otg_at_time(tr, t)
+            for j in held:
+                assert q[j] == a[j] and v[j] == 0.0 and acc[j] == 0.0
+            assert np.all(np.abs(v) <= m[1] * np.array(lim.vmax) * (1 + 1e-9)) and np.all(np.abs(acc) <= m[2] * np.array(lim.amax) * (1 + 1e-9))
+        q, v, acc = M.otg_at_time(tr, tr.T)
+        assert np.abs(q - b[:7]).max() < 1e-9 and np.abs(v).max() < 1e-9
+        # the warm start of the OCP samples the same profile (no cubic-Hermite fallback)
+        gx, gu, gT = M.guess_batch(s, lim, a[None], b[None])
+        assert abs(gT[0] - tr.T) < 1e-12
+        assert np.abs(gx[0].reshape(19, 14)[:, held] - a[held]).max() == 0.0
+    # nothing moves at all: duration 0 is not a usable guess for the final time, the fallback profile takes over
+    rc, tr = M.otg_calculate(lim, x0, x0)
+    assert rc >= 0 and tr.T == 0.0
+    gx, gu, gT = M.guess_batch(s, lim, x0[None], x0[None])
+    assert gT[0] > 0 and np.abs(gx[0].reshape(19, 14) - x0).max() < 1e-12

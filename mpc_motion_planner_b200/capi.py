@@ -257,6 +257,13 @@ class Solver:
         self._check(rc, "mpcb_sample_batch")
         return traj, acc
 
+    def sample_device(self, n, sx, su, sT, target, npts, traj, acc, stream=0):
+        """Device-pointer form of the read-out + accounting (raw addresses; traj or acc may be 0); only enqueues the kernel."""
+        rc = self.L.mpcb_sample_batch(self.h, C.c_int(n), _p(sx), _p(su), _p(sT), _p(target) if target else None, C.c_int(npts),
+                                      _p(traj) if traj else None, _p(acc) if acc else None, C.c_int(MEM_DEVICE),
+                                      C.c_void_p(stream) if stream else None)
+        self._check(rc, "mpcb_sample_batch")
+
     def last_solve_ms(self):
         return self.L.mpcb_last_solve_ms(self.h)
 

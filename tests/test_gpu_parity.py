@@ -159,6 +159,24 @@ def test_device_resident_pipeline(solver):
     assert np.array_equal(dstats["status"], st["status"]) and np.array_equal(dstats["qp_iters_total"], st["qp_iters_total"])
 
 
+def test_device_warm_start_stationary_joints(solver):
+    """Joints that do not move get a 'stay' profile on the device too (otg_guess_kernel), not the cubic-Hermite fallback."""
+    s, lim, x0, xT, gx, gu, gT = _problems(1, 11, 6, OFFLINE_MARGINS)
+    x0 = x0.copy(); xT = xT.copy()
+    x0[:, 7:] = 0.0; xT[:, 7:] = 0.0
+    for i, held in enumerate(([3], [1, 2, 3, 4, 5, 6], [0, 6], [], [2, 5], [0, 1, 2, 3, 4, 5])):
+        xT[i, held] = x0[i, held]
+    gx, gu, gT = M.guess_batch(s, lim, x0, xT)
+    solver.set_limits(lim)
+    dx, du, dT = solver.guess(x0, xT)
+    assert np.abs(dT - gT).max() <= 1e-12 * np.abs(gT).max()
+    assert np.abs(dx - gx).max() < 1e-10 and np.abs(du - gu).max() < 1e-8
+    assert np.array_equal(dx.reshape(6, 19, 14)[1, :, 1:7], np.broadcast_to(x0[1, 1:7], (19, 6)))
+    for i in range(6):
+        rc, tr = M.otg_calculate(lim, x0[i], xT[i])
+        assert rc >= 0 and abs(tr.T - dT[i]) <= 1e-12 * tr.T          # a jerk-limited profile, not the fallback
+
+
 def test_receding_horizon_resolve(oracle, solver):
     """BASELINE config 5: re-solve 1 ms later, warm-started from the previous solution INCLUDING its multipliers
     (motionPlanner.cpp:199-207 re-seed + polympc's dual carry-over) -- the guess_lam / sol_lam arguments."""

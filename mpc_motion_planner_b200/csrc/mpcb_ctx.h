@@ -95,7 +95,7 @@ struct Layout {   // offsets in doubles into the dynamic shared-memory block
     // The matrix area (W | F | C | BB) sits in shared memory when it fits (the base shape); for the larger collocation shapes
     // it lives in a per-CTA block of global memory (Ctx::bind gets the pointer) and only vectors + Jacobians stay on chip.
     static constexpr bool GMAT = (SH::MATSIZE + SH::BBSIZE) > 22000;
-    static constexpr int MATDOUBLES = SH::MATSIZE + SH::BBSIZE;
+    static constexpr int MATDOUBLES = SH::MATSIZE + SH::BBSIZE + SH::FULLSIZE;     // per-CTA global block: packed factors + full copies
     static constexpr int MAT = 0;                                  // W | F | C   (also: QP result)
     static constexpr int W = MAT, F = W + SH::WSIZE, C = F + SH::FSIZE;
     static constexpr int BB = MAT + SH::MATSIZE;
@@ -131,6 +131,7 @@ template <class SH>
 struct Ctx {
     double* sm;                    // shared-memory block
     double *W, *F, *C, *BB, *Jg, *w, *rhs, *xt, *Ha, *pcol, *part, *psum, *colbuf, *lims, *scal;
+    double *Wf, *Fc, *Cf;          // full copies of the operators (global block; generic ADMM path only, null otherwise)
     unsigned long long* umax;
     long long* isc;
     double* z;                     // global workspace: iterate, kernel order (NVAR)
@@ -152,6 +153,7 @@ struct Ctx {
         sm = smem;
         double* mat = L::GMAT ? gmat : sm + L::MAT;
         W = mat; F = mat + SH::WSIZE; C = F + SH::FSIZE; BB = mat + SH::MATSIZE; Jg = sm + L::JG; w = sm + L::VW; rhs = sm + L::VRHS;
+        Wf = L::GMAT ? gmat + SH::MATSIZE + SH::BBSIZE : nullptr; Fc = L::GMAT ? Wf + SH::WFSIZE : nullptr; Cf = L::GMAT ? Fc + SH::FSIZE : nullptr;
         xt = sm + L::VXT; Ha = sm + L::HA; pcol = sm + L::PCOL; part = sm + L::PART; psum = sm + L::PSUM;
         colbuf = sm + L::COLBUF; lims = sm + L::LIMS; scal = sm + L::SCAL;
         umax = reinterpret_cast<unsigned long long*>(sm + L::UMAX);
@@ -176,6 +178,9 @@ struct TS {
     // ---- factorisation: the 5 x 5 tile of an augmented segment matrix this thread sweeps in registers (mpcb_qp.h)
     double tile[25];
     int tI, tJ, tseg;
+#ifdef MPCB_EMUL
+    double acc;                  // host emulation of a cross-lane exchange (mpcb_gadmm.h)
+#endif
 };
 
 // ---- small helpers ------------------------------------------------------------------------------------------------

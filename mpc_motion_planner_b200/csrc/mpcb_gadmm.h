@@ -87,8 +87,73 @@ MPCB_DEV void g_rhs(Ctx<SH>& c, TS<SH>& ts, int tid) {
     }
     g_pcol_partial(c, tid, c.w, c.psum);
 }
+// Larger shapes (Layout::GMAT): the packed factors are expanded once per factorisation into full, coalesced copies -- W_s as a
+// square m x m array (thread = row l reads Wf[j m + l]: consecutive threads, consecutive addresses), F_s column-major (thread = row
+// reads Fc[col m + i]), C square -- so that every operator load of the iteration is a full 256-byte warp request.
+template <class SH>
+MPCB_DEV void g_expand(Ctx<SH>& c, int tid) {
+    if constexpr (Layout<SH>::GMAT) {
+        for (int s = 0; s < SH::NS; s++) {
+            const int m = SH::m(s), nb = SH::nb(s);
+            const double* Wn = c.W + SH::woff(s);
+            double* Wf = c.Wf + SH::wfoff(s);
+            for (int e = tid; e < m * m; e += SH::NT) {
+                const int j = e / m, l = e - j * m, hi = l > j ? l : j, lo = l > j ? j : l;
+                Wf[e] = Wn[hi * (hi + 1) / 2 + lo];
+            }
+            const double* Fs = c.F + SH::foff(s);
+            double* Fc = c.Fc + SH::foff(s);
+            for (int e = tid; e < m * nb; e += SH::NT) {
+                const int col = e / m, i = e - col * m;
+                Fc[e] = Fs[i * nb + col];
+            }
+        }
+        for (int e = tid; e < SH::NB * SH::NB; e += SH::NT) {
+            const int j = e / SH::NB, b = e - j * SH::NB, hi = b > j ? b : j, lo = b > j ? j : b;
+            c.Cf[e] = c.C[hi * (hi + 1) / 2 + lo];
+        }
+    }
+}
 template <class SH>
 MPCB_DEV void g_solve1(Ctx<SH>& c, TS<SH>& ts, int tid) {
+    if constexpr (Layout<SH>::GMAT) {
+        if (tid < SH::NI) {      // t = -(Wn rhs_I) from the full copy, four accumulators
+            const int s = ts.vseg, l = ts.vloc, m = SH::m(s);
+            const double* Wf = c.Wf + SH::wfoff(s) + l;
+            const double* b = c.rhs + SH::ioff(s);
+            double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+            int j = 0;
+            for (; j + 8 <= m; j += 8) {                 // eight operator loads in flight per thread: the stream is latency-bound otherwise
+                const double* wj = Wf + j * m;
+                const double w0 = wj[0], w1 = wj[m], w2 = wj[2 * m], w3 = wj[3 * m], w4 = wj[4 * m], w5 = wj[5 * m], w6 = wj[6 * m], w7 = wj[7 * m];
+                a0 += w0 * b[j]; a1 += w1 * b[j + 1]; a2 += w2 * b[j + 2]; a3 += w3 * b[j + 3];
+                a0 += w4 * b[j + 4]; a1 += w5 * b[j + 5]; a2 += w6 * b[j + 6]; a3 += w7 * b[j + 7];
+            }
+            for (; j < m; j++) a0 += Wf[j * m] * b[j];
+            c.xt[tid] = -((a0 + a1) + (a2 + a3));
+        }
+        for (int e = tid - SH::NI; e >= 0 && e < SH::PARTSIZE; e += SH::NT) {      // F_s^T rhs_I, one boundary column per thread
+            int s = 0, col = e;
+            while (col >= SH::nb(s)) { col -= SH::nb(s); s++; }
+            const int m = SH::m(s), nb = SH::nb(s);
+            const double* Fs = c.F + SH::foff(s) + col;          // row-major F: the threads of a segment read consecutive columns
+            const double* b = c.rhs + SH::ioff(s);
+            double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+            int i = 0;
+            for (; i + 4 <= m; i += 4) {
+                const double f0 = Fs[i * nb], f1 = Fs[(i + 1) * nb], f2 = Fs[(i + 2) * nb], f3 = Fs[(i + 3) * nb];
+                a0 += f0 * b[i]; a1 += f1 * b[i + 1]; a2 += f2 * b[i + 2]; a3 += f3 * b[i + 3];
+            }
+            for (; i < m; i++) a0 += Fs[i * nb] * b[i];
+            c.part[e] = (a0 + a1) + (a2 + a3);
+        }
+        if (tid == SH::NT - 1) {
+            double s = 0;
+            for (int j = 0; j < 32; j++) s += c.psum[j];
+            c.rhs[SH::IP] += s;
+        }
+        return;
+    }
     if (tid < SH::NI) {      // t = -(Wn rhs_I), symmetric packed row/column walk
         const int s = ts.vseg, l = ts.vloc, m = SH::m(s);
         const double* Wn = c.W + SH::woff(s);
@@ -139,10 +204,22 @@ MPCB_DEV void g_solve2a(Ctx<SH>& c, int tid) {
     if (tid < SH::NB) c.colbuf[tid] = g_sep_rhs(c, tid);
 }
 template <class SH>
-MPCB_DEV void g_solve2b(Ctx<SH>& c, int tid) {       // x~_B = -(Cn r), one thread per row, symmetric packed row/column walk
+MPCB_DEV void g_solve2b(Ctx<SH>& c, int tid) {       // x~_B = -(Cn r), one thread per row
     if (tid >= SH::NB) return;
     const int b = tid;
     const double* r = c.colbuf;
+    if constexpr (Layout<SH>::GMAT) {                  // full copy: thread b reads Cf[j NB + b]
+        const double* Cf = c.Cf + b;
+        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        int j = 0;
+        for (; j + 4 <= SH::NB; j += 4) {
+            const double c0 = Cf[j * SH::NB], c1 = Cf[(j + 1) * SH::NB], c2 = Cf[(j + 2) * SH::NB], c3 = Cf[(j + 3) * SH::NB];
+            a0 += c0 * r[j]; a1 += c1 * r[j + 1]; a2 += c2 * r[j + 2]; a3 += c3 * r[j + 3];
+        }
+        for (; j < SH::NB; j++) a0 += Cf[j * SH::NB] * r[j];
+        c.xt[SH::NI + b] = -((a0 + a1) + (a2 + a3));
+        return;
+    }
     const double* row = c.C + b * (b + 1) / 2;
     double a0 = 0, a1 = 0;
     int j = 0;
@@ -156,8 +233,18 @@ template <class SH>
 MPCB_DEV void g_solve3(Ctx<SH>& c, TS<SH>& ts, int tid) {     // x~_I = t - F x~_B
     if (tid >= SH::NI) return;
     const int s = ts.vseg, nb = SH::nb(s);
-    const double* Fr = c.F + SH::foff(s) + ts.vloc * nb;
     const double* xb = c.xt + SH::NI;
+    if constexpr (Layout<SH>::GMAT) {                  // column-major copy: thread = row i reads Fc[col m + i]
+        const int m = SH::m(s);
+        const double* Fc = c.Fc + SH::foff(s) + ts.vloc;
+        double a0 = 0, a1 = 0;
+        int col = 0;
+        if (s > 0) { const double* x1 = xb + 14 * (s - 1); for (int cc = 0; cc < 14; cc += 2) { a0 += Fc[(col + cc) * m] * x1[cc]; a1 += Fc[(col + cc + 1) * m] * x1[cc + 1]; } col += 14; }
+        if (s < SH::NS - 1) { const double* x2 = xb + 14 * s; for (int cc = 0; cc < 14; cc += 2) { a0 += Fc[(col + cc) * m] * x2[cc]; a1 += Fc[(col + cc + 1) * m] * x2[cc + 1]; } col += 14; }
+        c.xt[tid] -= (a0 + a1) + Fc[col * m] * xb[SH::NB - 1];
+        return;
+    }
+    const double* Fr = c.F + SH::foff(s) + ts.vloc * nb;
     double acc = 0;
     int col = 0;
     if (s > 0) { const double* x1 = xb + 14 * (s - 1); for (int cc = 0; cc < 14; cc++) acc += Fr[col + cc] * x1[cc]; col += 14; }
@@ -264,6 +351,7 @@ template <class SH>
 MPCB_DEV void solve_qp_generic(MPCB_DRIVER_PARAMS(SH), double* res) {
     MPCB_PROF_DECL
     factorise<SH>(MPCB_DRIVER_ARGS);
+    MPCB_PHASE(g_expand(c, tid));
     MPCB_PROF(25)
     MPCB_PHASE(g_init(c, ts, tid));
     const int max_iter = c.st->qp_max_iter, chk = c.st->qp_check_termination;
@@ -282,6 +370,7 @@ MPCB_DEV void solve_qp_generic(MPCB_DRIVER_PARAMS(SH), double* res) {
             if (c.isc[IS_REFAC]) {
                 MPCB_PHASE(g_rerho(c, ts, tid));
                 factorise<SH>(MPCB_DRIVER_ARGS);
+                MPCB_PHASE(g_expand(c, tid));
             }
         }
     }

@@ -57,6 +57,11 @@ struct Shape {
     static constexpr int BBSIZE = (NS == 1) ? 1 : 2 * tri(NB0) + (NS - 2) * tri(NBM);
     static constexpr int PARTSIZE = (NS == 1) ? 1 : 2 * NB0 + (NS - 2) * NBM;
     static constexpr int MATSIZE = WSIZE + FSIZE + CSIZE;
+    // full (square, coalesced) copies of the operators for the shape-generic ADMM iteration (mpcb_gadmm.h): W_s as m x m, F_s
+    // column-major (m x nb), C as NB x NB
+    MPCB_HD static int wfoff(int s) { int o = 0; for (int t = 0; t < s; t++) o += m(t) * m(t); return o; }
+    static constexpr int WFSIZE = (NS == 1) ? (MB + 35) * (MB + 35) : (MB + 14) * (MB + 14) + (NS - 2) * MB * MB + (MB + 21) * (MB + 21);
+    static constexpr int FULLSIZE = WFSIZE + FSIZE + NB * NB;
 
     // separator index (0..NB-1) of boundary column `col` of segment s
     MPCB_HD static int bsep(int s, int col) {

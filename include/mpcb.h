@@ -149,6 +149,11 @@ int mpcb_last_kernel_launches(const mpcb_handle* h, int kind);
  * 20 separator, 21 export, 22 merit + line search, 23 step + termination, 24 store, 25 factorise tail. */
 int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out512, int reset);   /* 512 slots; 64.. = per-warp stamps */
 
+/* Debug / per-function parity tests: minTime_ocp::evalConstraints<double> and <ad_scalar_t> (robot_ocp.hpp:80-163) exactly as the
+ * node kernels evaluate them, for n arbitrary states.  qva: n x 21 (q, v, a); g_val: n x 8 from the value pass; g_jac: n x 8 and
+ * Jg: n x 8 x 22 from the derivative pass.  Host pointers. */
+int mpcb_debug_node_constraints(mpcb_handle* h, int n, const double* qva, double* g_val, double* g_jac, double* Jg);
+
 /* FP64 FMA peak micro-benchmark on the handle's device (roofline denominator); returns TFLOP/s. */
 double mpcb_measure_fp64_tflops(mpcb_handle* h);
 

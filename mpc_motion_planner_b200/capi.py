@@ -264,6 +264,13 @@ class Solver:
                                       C.c_void_p(stream) if stream else None)
         self._check(rc, "mpcb_sample_batch")
 
+    def debug_node_constraints(self, qva):
+        """Per-node device functions on n states (q, v, a): (g from the value pass, g from the derivative pass, Jg (n, 8, 22))."""
+        qva = _d(np.atleast_2d(qva)); n = qva.shape[0]
+        gv = np.zeros((n, 8)); gj = np.zeros((n, 8)); Jg = np.zeros((n, 8, 22))
+        self._check(self.L.mpcb_debug_node_constraints(self.h, C.c_int(n), _p(qva), _p(gv), _p(gj), _p(Jg)), "mpcb_debug_node_constraints")
+        return gv, gj, Jg
+
     def last_solve_ms(self):
         return self.L.mpcb_last_solve_ms(self.h)
 

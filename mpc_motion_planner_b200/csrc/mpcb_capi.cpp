@@ -447,6 +447,27 @@ int mpcb_last_kernel_launches(const mpcb_handle* h, int kind) {
     return c;
 }
 
+int mpcb_debug_node_constraints(mpcb_handle* h, int n, const double* qva, double* g_val, double* g_jac, double* Jg) {
+    if (!h || n < 0 || (n > 0 && (!qva || !g_val || !g_jac || !Jg))) return MPCB_ERR_BAD_ARG;
+    if (n == 0) return MPCB_OK;
+    CK(cudaSetDevice(h->device));
+    const size_t bin = sizeof(double) * 21 * n, bg = sizeof(double) * 8 * n, bj = sizeof(double) * 176 * n;
+    int rc = ensure_stage(h, al(bin) + 2 * al(bg) + al(bj));
+    if (rc) return rc;
+    char* p = (char*)h->d_stage;
+    double* din = (double*)p; p += al(bin);
+    double* dv = (double*)p; p += al(bg);
+    double* dg = (double*)p; p += al(bg);
+    double* dj = (double*)p;
+    CK(cudaMemcpy(din, qva, bin, cudaMemcpyHostToDevice));
+    CK(launch_node_debug(n, din, dv, dg, dj, 0));
+    h->launches += 1;
+    CK(cudaMemcpy(g_val, dv, bg, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(g_jac, dg, bg, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(Jg, dj, bj, cudaMemcpyDeviceToHost));
+    return MPCB_OK;
+}
+
 double mpcb_measure_fp64_tflops(mpcb_handle* h) {
     if (!h) return -1.0;
     cudaSetDevice(h->device);

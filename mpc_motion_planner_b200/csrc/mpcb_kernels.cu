@@ -321,6 +321,21 @@ gen_problems_kernel(const __grid_constant__ mpcb_limits lim, const int kind, con
     for (int k = 0; k < 14; k++) { x0[(size_t)14 * i + k] = a[k]; xT[(size_t)14 * i + k] = b[k]; }
 }
 
+// ---- debug: the per-node device functions on arbitrary states (per-function parity tests) -------------------
+__global__ void __launch_bounds__(NODE_NT)
+node_debug_kernel(const int n, const double* __restrict__ qva, double* __restrict__ g_val, double* __restrict__ g_jac, double* __restrict__ Jg) {
+    const int i = blockIdx.x * NODE_NT + threadIdx.x;
+    if (i >= n) return;
+    double q[7], v[7], a[7], g[8], J[176];
+    for (int j = 0; j < 7; j++) { q[j] = qva[21 * i + j]; v[j] = qva[21 * i + 7 + j]; a[j] = qva[21 * i + 14 + j]; }
+    rbd::node_constraints_value(q, v, a, g);
+    for (int j = 0; j < 8; j++) g_val[8 * i + j] = g[j];
+    rbd::DerivScratch S;
+    rbd::node_constraints_jac(q, v, a, S, g, J);
+    for (int j = 0; j < 8; j++) g_jac[8 * i + j] = g[j];
+    for (int j = 0; j < 176; j++) Jg[176 * (size_t)i + j] = J[j];
+}
+
 // ---- FP64 FMA peak ---------------------------------------------------------------------------------------------------
 __global__ void fp64_peak_kernel(double* out, int iters) {
     double a0 = threadIdx.x * 1e-3, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
@@ -419,6 +434,10 @@ cudaError_t launch_otg_guess(const OtgConst& oc, int n, const double* x0, const 
 cudaError_t launch_gen_problems(const mpcb_limits& lim, int kind, unsigned long long seed, unsigned long long first, int n, double* x0, double* xT,
                                 cudaStream_t stream) {
     gen_problems_kernel<<<(unsigned)((n + GEN_NT - 1) / GEN_NT), GEN_NT, 0, stream>>>(lim, kind, seed, first, n, x0, xT);
+    return cudaGetLastError();
+}
+cudaError_t launch_node_debug(int n, const double* qva, double* g_val, double* g_jac, double* Jg, cudaStream_t stream) {
+    node_debug_kernel<<<(unsigned)((n + NODE_NT - 1) / NODE_NT), NODE_NT, 0, stream>>>(n, qva, g_val, g_jac, Jg);
     return cudaGetLastError();
 }
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream) {

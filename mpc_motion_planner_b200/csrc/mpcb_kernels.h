@@ -54,6 +54,8 @@ cudaError_t launch_otg_guess(const OtgConst& oc, int n, const double* x0, const 
 // problem generator: problem i of the launch draws from stream (seed, first + i)
 cudaError_t launch_gen_problems(const mpcb_limits& lim, int kind, unsigned long long seed, unsigned long long first, int n, double* x0, double* xT,
                                 cudaStream_t stream);
+// debug: node_constraints_value / node_constraints_jac of n states (q, v, a) on the device
+cudaError_t launch_node_debug(int n, const double* qva, double* g_val, double* g_jac, double* Jg, cudaStream_t stream);
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream);
 
 }  // namespace mpcb

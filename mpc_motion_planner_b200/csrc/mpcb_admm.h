@@ -3,7 +3,8 @@
 // (/root/reference/mpc_solver/motionPlanner.cpp:15-20,184).
 //
 //   rhs   = sigma x - h + rho_b z_b - y_b + A^T (rho_A z_A - y_A)                                   phase A
-//   x~    = S^-1 rhs  via  t = W rhs_I, part = F^T rhs_I | x~_B = C^-1 (rhs_B - part) | x~_I = t - F x~_B    phases B, B', C, D
+//   x~    = S^-1 rhs  via  t = W rhs_I | part = S_BI t (= F^T rhs_I, but sparse) | x~_B = C^-1 (rhs_B - part) | x~_I = t - F x~_B
+//                                                                                                     phases B, B', C, D
 //   z~_A  = A x~ ; x = a x~ + (1-a) x ; z = clip(a z~ + (1-a) z + y/rho) ; y += rho (a z~ + (1-a) z_old - z)   phase E
 // Every `check_termination` iterations the OSQP residual test runs (chk_*).
 //
@@ -27,7 +28,13 @@ template <class SH>
 struct AL {
     static_assert(SH::PO == 3 && SH::NS == 6, "the ADMM kernel's thread mapping is specialised for POLY_ORDER=3, NUM_SEG=6");
     static constexpr int SEG = 66, NV = 416, IP = 414;  // padded node order: segment stride, length, index of p
-    static constexpr int WREG = 32;                    // W coefficients per thread held in registers
+#ifndef MPCB_ADMM_WIDE
+#define MPCB_ADMM_WIDE 1                               // 1: one logical thread per physical thread (512 x 128 registers); 0: two (256 x 255)
+#endif
+    // W coefficients per thread held in registers; the rest of a thread's block sits in its TMEM strip in chunks of 16
+    static constexpr int WREG = MPCB_ADMM_WIDE ? 20 : 32;
+    // number of 16-slot overflow chunks of the three thread kinds (segment 0: 32 coefficients, middle: 49, segment 5: 36)
+    MPCB_HD static constexpr int wchunks(int kind) { return ((kind == 0 ? 32 : (kind == 1 ? 49 : 36)) - WREG + 15) / 16; }
     // ---- shared-memory image (copied verbatim from the global QP block) --------------------------------------------
     // inequality Jacobian, twice: row-major for A x (row stride 26, node stride 208; a row starts one slot late when its
     // node's first variable sits on an odd index, so that 16-byte loads of the row line up with 16-byte loads of x) and
@@ -41,22 +48,25 @@ struct AL {
     static constexpr int I_PCV = I_PCOL + 256;         // A[r, p] of every row r (416, zero padded)
     static constexpr int I_FPC = I_PCV + 416;          // F_s[row, p] at the padded-node-order index of the interior variable (416)
     static constexpr int I_DT = I_FPC + 416;           // D (16) | -ts*pbar | pad
-    static constexpr int IMG = I_DT + 24;
+    static constexpr int I_SBI = I_DT + 24;            // S_BI units: [SBI_E][SBI_T] coefficients (phase B')
+    static constexpr int IMG = I_SBI + 7 * 288;
     // ---- thread-private strips in tensor memory (mpcb_tmem.h), slot = one double -----------------------------------
-    //   warps 0..3   (segment-0 row pairs) : consts 0..7 | F half row 8..15 | F^T chunk 16..33 | C^-1 quarter row 34..51
-    //   warps 4..10  (middle-segment rows) : consts 0..7 | W columns 32..48 8..24 | F row 25..53 | F^T chunk 54..71
-    //   warps 11..15 (segment-5 row pairs) : consts 0..7 | W tail 8..11 | F half row 12..19 | F^T chunk 20..37 | C^-1 quarter row 38..55
+    //   warps 0..3   (segment-0 blocks) : consts 0..7 | W overflow chunks | F half row (8) | C^-1 quarter row (18)
+    //   warps 4..10  (middle blocks)    : consts 0..7 | W overflow chunks | F row (29)
+    //   warps 11..15 (segment-5 blocks) : consts 0..7 | W overflow chunks | F half row (8) | C^-1 quarter row (18)
     // consts = l, u, rho, 1/rho of the thread's row | lb, ub, rho_b, 1/rho_b of the thread's variable
     static constexpr int TM_CST = 0;
     MPCB_HD static int tm_size(int w) { return (w >= 4 && w <= 10) ? 72 : 56; }
     MPCB_HD static int tm_wov(int tid) { return 8; }
-    MPCB_HD static int tm_frow(int tid) { return tid < 128 ? 8 : (tid < 352 ? 25 : 12); }
-    MPCB_HD static int tm_ft(int tid) { return tid < 128 ? 16 : (tid < 352 ? 54 : 20); }
-    MPCB_HD static int tm_c(int tid) { return tid < 128 ? 34 : 38; }
+    MPCB_HD static int tm_frow(int tid) { return 8 + 16 * wchunks(tid < 128 ? 0 : (tid < 352 ? 1 : 2)); }
+    MPCB_HD static int tm_c(int tid) { return tm_frow(tid) + 8; }
+    static_assert(8 + 16 * wchunks(0) + 8 + 18 <= 56 && 8 + 16 * wchunks(1) + 29 <= 72 && 8 + 16 * wchunks(2) + 8 + 18 <= 56, "TMEM strips");
     // C^-1 unit of a thread (4 units per separator row): threads 0..127 and 352..511, -1 elsewhere / beyond 4 NB
     MPCB_HD static int cunit(int tid) { const int u = tid < 128 ? tid : (tid >= 352 ? tid - 224 : -1); return u < 4 * SH::NB ? u : -1; }
     // ---- working vectors behind the image --------------------------------------------------------------------------
-    static constexpr int V_RHS = IMG, V_XT = V_RHS + NV, V_W = V_XT + NV, V_PARTF = V_W + NV, V_RB = V_PARTF + 472;
+    // S_BI units (phase B'): 4 lanes per junction variable, SBI_E candidate entries per lane; V_SBI holds their vector indices (ints)
+    static constexpr int SBI_T = 288, SBI_E = 7;
+    static constexpr int V_RHS = IMG, V_XT = V_RHS + NV, V_W = V_XT + NV, V_SBI = V_W + NV, V_RB = V_SBI + (SBI_T * SBI_E + 1) / 2;
     static constexpr int V_PSUM = V_RB + 72, V_SC = V_PSUM + 64, V_UMAX = V_SC + 8, V_ISC = V_UMAX + UM_COUNT;
     static constexpr int PTID = 416;                   // thread that owns the variable p (lane 0 of warp 13)
     static constexpr int TOTAL = V_ISC + 8;
@@ -84,79 +94,102 @@ struct AL {
     }
 };
 
-// Role of a thread in the interior mat-vecs (phases B and D): which row of which W_s, and which columns it covers.
-//   segments 0 and 5: two lanes per row; lane `half` takes the 16-byte column chunks 2 q + half (q = 0, 1, ..), so the pair
-//                     reads one contiguous 32-byte piece of the vector per step
-//   middle segments : one lane per row, all 49 columns (32 from registers, 17 from shared memory)
+// Role of a thread in the interior mat-vecs (phases B and D).
+//   Phase B (t = W rhs_I) works on BLOCKS: 8 lanes share a group of R rows of one W_s; lane q multiplies the columns q, q + 8,
+//   q + 16, .. of all R rows (R independent accumulators, one shared-memory load of the vector entry per R multiply-adds; the 8
+//   lanes of a group read 8 consecutive vector entries per step), then a transpose-reduce over the 8 lanes (xor 4, 2, 1) leaves
+//   every lane with the full sum of ONE row:
+//       segment 0      : 16 groups of R = 4 rows, 8 column steps  -> 32 coefficients per thread (registers)
+//       middle segments: 7 groups of R = 7 rows, 7 column steps   -> 49 coefficients per thread (32 registers + 17 TMEM)
+//       segment 5      : 18 groups of R = 4 rows, 9 column steps  -> 36 coefficients per thread (32 registers + 4 TMEM)
+//   The row a lane ends up with is the row it owns in phase D (x~_I = t - F x~_B): with R = 4 two lanes end with the same row
+//   and split its F row in halves (paired), with R = 7 one lane per row (the eighth lane of the group idles in phase D).
 struct WRole {
-    bool valid, paired;
+    bool valid, paired;     // phase D: the lane owns (half of) row `row`
     int seg, row, half;
-    int out;         // padded-node-order index of the row
+    int out;                // padded-node-order index of the row
+    int kind;               // 0: segment 0, 1: middle segment, 2: segment 5
+    int grow0, q;           // phase B: first row of the lane's group, column lane
 };
 template <class SH>
 MPCB_HD WRole wrole(int tid) {
     typedef AL<SH> L;
     WRole r;
+    r.q = tid & 7;
+    const int b2 = (r.q >> 2) & 1, b1 = (r.q >> 1) & 1, b0 = r.q & 1;
     if (tid < 128) {
-        r.seg = 0; r.row = tid >> 1; r.half = tid & 1; r.valid = r.row < 63; r.paired = true; r.out = r.row;
+        r.kind = 0; r.seg = 0; r.grow0 = 4 * (tid >> 3);
+        r.row = r.grow0 + 2 * b2 + b1; r.half = b0; r.paired = true; r.valid = r.row < 63; r.out = r.row;
     } else if (tid < 352) {
         const int idx = tid - 128;
-        r.valid = idx < 196; r.paired = false; r.half = 0;
-        r.seg = 1 + idx / 49; r.row = idx % 49;
-        if (!r.valid) { r.seg = 1; r.row = 0; }
+        r.kind = 1; r.seg = 1 + idx / 56; r.grow0 = 7 * ((idx % 56) >> 3);
+        const int rl = 4 * b2 + 2 * b1 + b0;
+        r.row = r.grow0 + rl; r.half = 0; r.paired = false; r.valid = rl < 7;
         r.out = L::SEG * r.seg + 14 + r.row;
     } else {
         const int idx = tid - 352;
-        r.seg = 5; r.row = idx >> 1; r.half = idx & 1; r.valid = idx < 140; r.paired = true;
-        if (!r.valid) r.row = 0;
+        r.kind = 2; r.seg = 5; r.grow0 = 4 * (idx >> 3);
+        r.row = r.grow0 + 2 * b2 + b1; r.half = b0; r.paired = true; r.valid = idx < 144 && r.row < 70;
         r.out = 5 * L::SEG + 14 + r.row;
     }
+    if (!r.valid) { r.row = 0; r.out = 0; }
     return r;
 }
-// column of W_seg that coefficient slot e of the thread multiplies (e < 32: registers, e >= 32: shared-memory overflow);
-// -1 for padding slots.  The exporter and the kernel share this map.
+// rows per group / column steps of the three kinds
+MPCB_HD int wrows(int kind) { return kind == 1 ? 7 : 4; }
+MPCB_HD int wsteps(int kind) { return kind == 0 ? 8 : (kind == 1 ? 7 : 9); }
+// (row, col) of W_seg that coefficient slot e of the thread multiplies: e = step * R + r (e < 32: registers, e >= 32: TMEM
+// overflow); false for padding slots.  The exporter and the kernel share this map.
 template <class SH>
-MPCB_HD int wcol(const WRole& r, int e) {
-    if (!r.valid) return -1;
-    const int col = r.paired ? 4 * (e >> 1) + 2 * r.half + (e & 1) : e;
-    return col < SH::m(r.seg) ? col : -1;
+MPCB_HD bool wslot(const WRole& r, int tid, int e, int& row, int& col) {
+    const int R = wrows(r.kind);
+    if (e >= R * wsteps(r.kind) || (r.kind == 2 && tid >= 352 + 144)) return false;
+    row = r.grow0 + e % R; col = r.q + 8 * (e / R);
+    return row < SH::m(r.seg) && col < SH::m(r.seg);
 }
 
-// Role of a thread in part = F^T rhs_I (phase B): one column of one F_s over a chunk of at most 18 rows.
-// 468 units: segment 0 -> 4 chunks x 15 columns, middle segments -> 3 chunks x 29 columns, segment 5 -> 4 chunks x 15.
-struct FRole {
-    int unit;        // -1: none; else index into partF = pfoff(seg) + chunk * nb(seg) + col
-    int seg, col, r0, len;
-};
+// part = S_BI t (phase B'): the rows of the KKT matrix S that belong to the junction states x_{3 sj} (sj = 1..5), restricted to
+// the interior variables.  F^T rhs_I = S_BI W rhs_I = S_BI t, and S_BI is sparse: junction variable (3 sj, c) of joint j = c % 7
+// only meets (q_j, v_j, u_j) at the other nodes of its two segments (collocation rows of joint j) and the controls of its own
+// node (inequality rows of node 3 sj).  Candidate e = 0..24 of junction variable b = 14 (sj - 1) + c:
+//      0..1   x_{0, j}, x_{0, 7+j}                        (left segment is segment 0: its first state is interior)
+//      2      u_{3 sj - 3, j}
+//      3..8   (q_j, v_j, u_j) at nodes 3 sj - 2, 3 sj - 1
+//      9..15  u_{3 sj, 0..6}
+//      16..21 (q_j, v_j, u_j) at nodes 3 sj + 1, 3 sj + 2
+//      22..24 (q_j, v_j, u_j) at node 18                  (right segment is segment 5: the final node is interior)
+// A superset of the structural non-zeros (entries that are structurally zero carry a zero coefficient).  Four lanes share
+// one junction variable: lane q takes the candidates q, q + 4, .., q + 24.  The exporter and the kernel share this map.
 template <class SH>
-MPCB_HD int pfoff(int s) { return s == 0 ? 0 : (s == 5 ? 408 : 60 + 87 * (s - 1)); }
+MPCB_HD bool sbi_cand(int b, int e, int& seg, int& k, int& comp) {
+    const int sj = b / 14 + 1, c = b % 14, j = c % 7, kj = 3 * sj;
+    if (e < 9) {
+        seg = sj - 1;
+        if (e < 2) { k = 0; comp = e == 0 ? j : 7 + j; return sj == 1; }
+        if (e == 2) { k = kj - 3; comp = 14 + j; return true; }
+        const int q = e - 3;
+        k = kj - 2 + q / 3; comp = 7 * (q % 3) + j;
+        return true;
+    }
+    seg = sj;
+    if (e < 16) { k = kj; comp = 14 + (e - 9); return true; }
+    if (e < 22) { const int q = e - 16; k = kj + 1 + q / 3; comp = 7 * (q % 3) + j; return true; }
+    if (e < 25) { k = 18; comp = 7 * (e - 22) + j; return sj == 5; }
+    return false;
+}
+// boundary column of junction variable b = 14 (sj - 1) + c inside segment `seg` (sj - 1: its right junction, sj: its left junction)
 template <class SH>
-MPCB_HD int fchunks(int s) { return (s == 0 || s == 5) ? 4 : 3; }
-template <class SH>
-MPCB_HD FRole frole(int tid) {
-    // warps 0..11: one (middle segment, chunk) per warp, lane = column (29 of 32 lanes); warps 12..15: chunk w - 12 of
-    // segment 0 on lanes 0..14 and of segment 5 on lanes 16..30 -- every half-warp reads one F column stripe with an odd
-    // stride (conflict-free) and broadcasts its rhs chunk
-    // (written with selects, not early returns: the ADMM phase that uses it is straight-line code)
-    FRole f;
-    const int w = tid >> 5, lane = tid & 31;
-    const bool mid = w < 12, lo = lane < 16;
-    const int ch = mid ? w % 3 : w - 12;
-    f.seg = mid ? 1 + w / 3 : (lo ? 0 : 5);
-    f.col = mid ? lane : (lane & 15);
-    f.r0 = mid ? (ch == 0 ? 0 : (ch == 1 ? 18 : 34)) : (lo ? 16 * ch : 18 * ch);
-    f.len = mid ? (ch == 0 ? 18 : (ch == 1 ? 16 : 15)) : (lo ? (ch == 3 ? 15 : 16) : (ch == 3 ? 16 : 18));
-    const bool valid = mid ? lane < 29 : (lane & 15) != 15;
-    f.unit = valid ? pfoff<SH>(f.seg) + ch * SH::nb(f.seg) + f.col : -1;
-    if (!valid) { f.len = 0; }
-    return f;
+MPCB_HD int sbi_col(int b, int seg) {
+    const int sj = b / 14 + 1, c = b % 14;
+    return seg == sj ? c : (seg > 0 ? 14 : 0) + c;
 }
 
 template <class SH>
 struct ACtx {
     double* sm;
-    double *Jg, *Gt, *hd, *ha, *pcol, *pcv, *fpc, *dt;
-    double *rhs, *xt, *w, *partF, *rB, *psum, *sc;
+    double *Jg, *Gt, *hd, *ha, *pcol, *pcv, *fpc, *dt, *sbc;
+    double *rhs, *xt, *w, *rB, *psum, *sc;
+    int* sbi;                      // [SBI_E][SBI_T] vector indices of the S_BI units
     unsigned long long* umax;
     long long* isc;
     double* g;                     // this OCP's QP block in global memory
@@ -166,8 +199,8 @@ struct ACtx {
         typedef AL<SH> L;
         sm = smem;
         Jg = sm + L::I_JG; Gt = sm + L::I_GT; hd = sm + L::I_HD;
-        ha = sm + L::I_HA; pcol = sm + L::I_PCOL; pcv = sm + L::I_PCV; fpc = sm + L::I_FPC; dt = sm + L::I_DT;
-        rhs = sm + L::V_RHS; xt = sm + L::V_XT; w = sm + L::V_W; partF = sm + L::V_PARTF; rB = sm + L::V_RB;
+        ha = sm + L::I_HA; pcol = sm + L::I_PCOL; pcv = sm + L::I_PCV; fpc = sm + L::I_FPC; dt = sm + L::I_DT; sbc = sm + L::I_SBI;
+        rhs = sm + L::V_RHS; xt = sm + L::V_XT; w = sm + L::V_W; sbi = reinterpret_cast<int*>(sm + L::V_SBI); rB = sm + L::V_RB;
         psum = sm + L::V_PSUM; sc = sm + L::V_SC;
         umax = reinterpret_cast<unsigned long long*>(sm + L::V_UMAX);
         isc = reinterpret_cast<long long*>(sm + L::V_ISC);
@@ -184,6 +217,7 @@ struct ATS {
     double x, zB, yB, rhoB;                // variable role (thread i < 404 in padded node order; p on thread PTID); lb, ub, 1/rho_b in TMEM
     double t, acc, acc2;                   // interior row: W rhs_I ; cross-lane exchange slots
 #ifdef MPCB_EMUL
+    double pv[8];                          // host emulation of the transpose-reduce of phase B: the lane's R partial sums
     double tm[TM_SLOTS];                   // host emulation of the thread's TMEM strip
     const double* tma() const { return tm; }
 #else
@@ -198,7 +232,7 @@ struct ATS {
 // next to the 2 x 64 registers of W coefficients (with 512 physical threads it had ~45, which serialised every phase into
 // load -> use round trips, profiles/r1j_admm_kernel_hotlines.txt).  Logical warps w and w + 8 share physical warp w: same
 // lanes (shuffles are unchanged) and the same TMEM lane quadrant (w % 4).
-constexpr int ANT = NT / 2;
+constexpr int ANT = MPCB_ADMM_WIDE ? NT : NT / 2;
 #ifdef MPCB_EMUL
 #define MPCB_ADRV_PARAMS(SH) ACtx<SH>& c, ATS<SH>* tsv
 #define MPCB_ADRV_ARGS c, tsv
@@ -207,11 +241,18 @@ constexpr int ANT = NT / 2;
 #else
 #define MPCB_ADRV_PARAMS(SH) ACtx<SH>& c, ATS<SH>& ts0, ATS<SH>& ts1, const int ptid
 #define MPCB_ADRV_ARGS c, ts0, ts1, ptid
+#if MPCB_ADMM_WIDE
+#define MPCB_APHASE_NS(...)                                                   \
+    {                                                                         \
+        { const int tid = ptid; ATS<SH>& ts = ts0; (void)ts; (void)tid; __VA_ARGS__; }   \
+    }
+#else
 #define MPCB_APHASE_NS(...)                                                   \
     {                                                                         \
         { const int tid = ptid; ATS<SH>& ts = ts0; (void)ts; (void)tid; __VA_ARGS__; }   \
         { const int tid = ptid + ANT; ATS<SH>& ts = ts1; (void)ts; (void)tid; __VA_ARGS__; } \
     }
+#endif
 #define MPCB_APHASE(...)             \
     {                                \
         MPCB_APHASE_NS(__VA_ARGS__)  \
@@ -361,7 +402,13 @@ MPCB_DEV void a_load(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     if (tid < L::NV) { c.rhs[tid] = 0; c.xt[tid] = 0; c.w[tid] = 0; }
     ts.zA = ts.yA = ts.x = ts.zB = ts.yB = ts.t = ts.acc = ts.acc2 = 0;     // boxADMM starts cold (warm_start = false)
     if (tid < 72) c.rB[tid] = 0;
-    if (tid < 472) c.partF[tid] = 0;
+    if (tid < L::SBI_T) {      // vector indices of the thread's S_BI candidates (static; absent candidates point at slot 0 with a zero coefficient)
+        for (int e = 0; e < L::SBI_E; e++) {
+            int seg, k, comp;
+            const bool ok = (tid >> 2) < SH::NB - 1 && sbi_cand<SH>(tid >> 2, (tid & 3) + 4 * e, seg, k, comp);
+            c.sbi[L::SBI_T * e + tid] = ok ? L::vidx(k, comp) : 0;
+        }
+    }
     if (tid < 64) c.psum[tid] = 0;
     if (tid < UM_COUNT) c.umax[tid] = 0;
     if (tid == 0) { c.isc[IS_QP_DONE] = 0; c.isc[IS_QP_STATUS] = 2; c.isc[IS_QP_ITERS] = 0; }
@@ -409,7 +456,7 @@ MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 }
 // (A^T w)_p = sum_r A[r,p] w_r in two steps that stay off the critical path: logical warp 14 (it owns no variable) forms
 // 32 strided partial sums here without the 5-step shuffle butterfly (~230 cycles of pure latency at the end of the
-// interval), a lane without an F^T unit adds them up in phase B1 (b_ft).  Measured: phase A -130 cycles, B1 +75.
+// interval), one lane adds them up in the next interval (b_w_finish).
 template <class SH>
 MPCB_DEV void a_rhs_p(ACtx<SH>& c, int tid) {
     if ((tid >> 5) != 14) return;
@@ -422,114 +469,112 @@ MPCB_DEV void a_rhs_p(ACtx<SH>& c, int tid) {
     c.psum[tid & 31] = (a0 + a1) + (a2 + a3);
 }
 
-// ---- phase B1: part = F^T rhs_I --------------------------------------------------------------------------------------
-template <class SH>
-MPCB_DEV void b_ft(ACtx<SH>& c, ATS<SH>& ts, int tid) {
-    typedef AL<SH> L;
-    const FRole f = frole<SH>(tid);
-    // the unit's 18 coefficients F_s[r0 + i, col] (zero beyond the chunk) come from the thread's TMEM strip; tcgen05.ld is
-    // warp-collective, so every lane loads (idle lanes hold zeros) and only the use is predicated
-    TmBuf<8> f0, f1;
-    TmBuf<2> f2;
-    const int so = L::tm_ft(tid);
-    tm_ld(ts.tma(), so, f0); tm_ld(ts.tma(), so + 8, f1); tm_ld(ts.tma(), so + 16, f2);
-    {
-        // the rhs chunk is read while the tensor-memory loads are in flight (the wait orders memory operations behind it)
-        const double* b = c.rhs + L::ibase(f.seg) + f.r0;
-        d2 v[9];
+// ---- phase B: t = W rhs_I from the register-resident rows ------------------------------------------------------------
+// transpose-reduce of R partial sums over the 8 lanes of a group: lane q ends with the full sum of local row
+// (R = 8: 4 b2 + 2 b1 + b0 ; R = 4: 2 b2 + b1, on both lanes of a pair) where b2 b1 b0 are the bits of q
+#ifndef MPCB_EMUL
+template <int R>
+__device__ __forceinline__ double wreduce(const double* v, int q) {
+    const bool h4 = q & 4, h2 = q & 2, h1 = q & 1;
+    if (R == 8) {
+        double u[4], w[2];
         MPCB_UNROLL
-        for (int i = 0; i < 9; i++) v[i] = ld2(b + 2 * i);
-        tm_wait(f0, f1, f2);
-        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        for (int i = 0; i < 4; i++) { const double keep = h4 ? v[4 + i] : v[i], send = h4 ? v[i] : v[4 + i]; u[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4); }
         MPCB_UNROLL
-        for (int i = 0; i < 8; i += 4) {
-            a0 += f0.get(i) * v[i / 2].a; a1 += f0.get(i + 1) * v[i / 2].b; a2 += f0.get(i + 2) * v[i / 2 + 1].a; a3 += f0.get(i + 3) * v[i / 2 + 1].b;
-        }
+        for (int i = 0; i < 2; i++) { const double keep = h2 ? u[2 + i] : u[i], send = h2 ? u[i] : u[2 + i]; w[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2); }
+        const double keep = h1 ? w[1] : w[0], send = h1 ? w[0] : w[1];
+        return keep + __shfl_xor_sync(0xffffffffu, send, 1);
+    } else {
+        double u[2];
         MPCB_UNROLL
-        for (int i = 0; i < 8; i += 4) {
-            a0 += f1.get(i) * v[4 + i / 2].a; a1 += f1.get(i + 1) * v[4 + i / 2].b; a2 += f1.get(i + 2) * v[5 + i / 2].a; a3 += f1.get(i + 3) * v[5 + i / 2].b;
-        }
-        a0 += f2.get(0) * v[8].a; a1 += f2.get(1) * v[8].b;
-        // the p column is summed through fpc (phase B') instead
-        if (f.unit >= 0 && f.col < SH::nb(f.seg) - 1) c.partF[f.unit] = (a0 + a1) + (a2 + a3);
-    }
-    if (tid == 31) c.sc[0] = tree32(c.psum);        // (A^T w)_p from the partial sums of phase A (a_rhs_p); lane 31 of warp 0 has no unit
-    if ((tid >> 5) == 15) {
-        // (F^T rhs_I)_p = sum_i F[i,p] rhs_i: 32 strided partial sums here, added up by the thread that forms r_B[p] in the
-        // next interval (b_seprhs) -- the same split as for (A^T w)_p, again to keep a shuffle butterfly off the longest path
-        const double* p = c.fpc + (tid & 31);
-        const double* q = c.rhs + (tid & 31);
-        double a0 = p[0] * q[0], a1 = p[32] * q[32], a2 = p[64] * q[64], a3 = p[96] * q[96];
-        a0 += p[128] * q[128]; a1 += p[160] * q[160]; a2 += p[192] * q[192]; a3 += p[224] * q[224];
-        a0 += p[256] * q[256]; a1 += p[288] * q[288]; a2 += p[320] * q[320]; a3 += p[352] * q[352];
-        a0 += p[384] * q[384];
-        c.psum[32 + (tid & 31)] = (a0 + a1) + (a2 + a3);
+        for (int i = 0; i < 2; i++) { const double keep = h4 ? v[2 + i] : v[i], send = h4 ? v[i] : v[2 + i]; u[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4); }
+        const double keep = h2 ? u[1] : u[0], send = h2 ? u[0] : u[1];
+        const double w = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+        return w + __shfl_xor_sync(0xffffffffu, w, 1);
     }
 }
-// ---- phase B2: t = W rhs_I from the register-resident rows (runs in the same barrier interval as the separator rhs) ---
+#endif
+// R x STEPS block of W times the vector: coefficient slot e = step * R + r comes from the registers (e < 32) or from the TMEM
+// overflow buffers (ov(e - 32))
+// multiply-adds of the coefficient slots [E0, E1) of an R x STEPS block: slot e = step * R + r multiplies x[step] into acc[r];
+// coef(e) delivers the coefficient (registers or a TMEM chunk)
+template <int R, int STEPS, int E0, int E1, class COEF>
+MPCB_DEV void w_slots(const double* x, const COEF& coef, double* acc) {
+    MPCB_UNROLL
+    for (int e = E0; e < (E1 < R * STEPS ? E1 : R * STEPS); e++) acc[e % R] += coef(e) * x[e / R];
+}
+// one thread's R x STEPS block of W times the vector: registers first, then the TMEM overflow chunk by chunk (16 slots each)
+template <class SH, int KIND, int R, int STEPS>
+MPCB_DEV void w_block(ACtx<SH>& c, ATS<SH>& ts, int tid, const double* b, double* acc) {
+    typedef AL<SH> L;
+    constexpr int W = L::WREG, NCH = L::wchunks(KIND);
+    TmBuf<16> ch0;
+    if constexpr (NCH > 0) tm_ld(ts.tma(), L::tm_wov(tid), ch0);
+    double x[STEPS];                                   // the vector entries are read while the tensor-memory load is in flight
+    MPCB_UNROLL
+    for (int t = 0; t < STEPS; t++) x[t] = b[8 * t];
+    w_slots<R, STEPS, 0, W>(x, [&](int e) { return ts.wreg[e]; }, acc);
+    if constexpr (NCH > 0) {
+        tm_wait(ch0);
+        w_slots<R, STEPS, W, W + 16>(x, [&](int e) { return ch0.get(e - W); }, acc);
+    }
+    if constexpr (NCH > 1) {
+        TmBuf<16> ch1;
+        tm_ld(ts.tma(), L::tm_wov(tid) + 16, ch1);
+        tm_wait(ch1);
+        w_slots<R, STEPS, W + 16, W + 32>(x, [&](int e) { return ch1.get(e - W - 16); }, acc);
+    }
+    static_assert(NCH <= 2, "at most two overflow chunks");
+}
 template <class SH>
 MPCB_DEV void b_w(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
     const WRole r = wrole<SH>(tid);
-    if (r.paired) {
-        const double* b = c.rhs + L::ibase(r.seg) + 2 * r.half;
-        TmBuf<4> wo;                                   // segment 5: columns 64 + 2 half, +1, 68 + 2 half, +1 of the row
-        if (r.seg == 5) tm_ld(ts.tma(), L::tm_wov(tid), wo);
-        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-        MPCB_UNROLL
-        for (int q = 0; q < 16; q += 2) {
-            const d2 v = ld2(b + 4 * q), v2 = ld2(b + 4 * q + 4);
-            a0 += ts.wreg[2 * q] * v.a; a1 += ts.wreg[2 * q + 1] * v.b; a2 += ts.wreg[2 * q + 2] * v2.a; a3 += ts.wreg[2 * q + 3] * v2.b;
-        }
-        if (r.seg == 5) {
-            const d2 v = ld2(b + 64), v2 = ld2(b + 68);
-            tm_wait(wo);
-            a0 += wo.get(0) * v.a; a1 += wo.get(1) * v.b; a2 += wo.get(2) * v2.a; a3 += wo.get(3) * v2.b;
-        }
-        ts.acc = (a0 + a1) + (a2 + a3);
-    } else {
-        const double* b = c.rhs + L::ibase(r.seg);
-        TmBuf<8> w0, w1;                               // columns 32..47 of the row
-        TmBuf<1> w2;                                   // column 48
-        const int so = L::tm_wov(tid);
-        tm_ld(ts.tma(), so, w0); tm_ld(ts.tma(), so + 8, w1); tm_ld(ts.tma(), so + 16, w2);    // in flight during the register part
-        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-        MPCB_UNROLL
-        for (int e = 0; e < L::WREG; e += 4) {
-            const d2 v = ld2(b + e), v2 = ld2(b + e + 2);
-            a0 += ts.wreg[e] * v.a; a1 += ts.wreg[e + 1] * v.b; a2 += ts.wreg[e + 2] * v2.a; a3 += ts.wreg[e + 3] * v2.b;
-        }
-        tm_wait(w0, w1, w2);
-        MPCB_UNROLL
-        for (int e = 0; e < 8; e += 4) {
-            const d2 v = ld2(b + 32 + e), v2 = ld2(b + 34 + e);
-            a0 += w0.get(e) * v.a; a1 += w0.get(e + 1) * v.b; a2 += w0.get(e + 2) * v2.a; a3 += w0.get(e + 3) * v2.b;
-        }
-        MPCB_UNROLL
-        for (int e = 0; e < 8; e += 4) {
-            const d2 v = ld2(b + 40 + e), v2 = ld2(b + 42 + e);
-            a0 += w1.get(e) * v.a; a1 += w1.get(e + 1) * v.b; a2 += w1.get(e + 2) * v2.a; a3 += w1.get(e + 3) * v2.b;
-        }
-        a0 += w2.get(0) * b[48];
-        ts.acc = (a0 + a1) + (a2 + a3);
-    }
+    const double* b = c.rhs + L::ibase(r.seg) + r.q;
+    double v[8];
+    MPCB_UNROLL
+    for (int i = 0; i < 8; i++) v[i] = 0;
+    if (r.kind == 0) w_block<SH, 0, 4, 8>(c, ts, tid, b, v);
+    else if (r.kind == 1) w_block<SH, 1, 7, 7>(c, ts, tid, b, v);
+    else w_block<SH, 2, 4, 9>(c, ts, tid, b, v);
+#ifdef MPCB_EMUL
+    for (int i = 0; i < 8; i++) ts.pv[i] = v[i];
+#else
+    ts.acc = r.kind == 1 ? wreduce<8>(v, r.q) : wreduce<4>(v, r.q);
+#endif
 }
-// ---- phase B': separator right-hand side r_B = rhs_B - sum_s (F_s^T rhs_I) -------------------------------------------
+// ---- phase B': separator right-hand side r_B = rhs_B - S_BI t (4 lanes per junction variable), r_B[p] -------------------------
 template <class SH>
-MPCB_DEV void b_seprhs(ACtx<SH>& c, int tid) {
+MPCB_DEV void b_sbi(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
-    {   // p: r_B[p] = rhs_p + (A^T w)_p - (F^T rhs_I)_p ; both dot products arrive as sums from phase B1
-        if (tid == 15 * 32) c.rB[SH::NB - 1] = (c.rhs[L::IP] + c.sc[0]) - tree32(c.psum + 32);
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    if (tid < L::SBI_T) {
+        // the unit's 7 coefficients S[b, cand] (zero for absent candidates / spare lanes) and the vector entries they multiply
+        const int* ix = c.sbi + tid;
+        const double* k = c.sbc + tid;
+        double tv[L::SBI_E], kv[L::SBI_E];
+        MPCB_UNROLL
+        for (int e = 0; e < L::SBI_E; e++) { tv[e] = c.xt[ix[L::SBI_T * e]]; kv[e] = k[L::SBI_T * e]; }
+        a0 += kv[0] * tv[0]; a1 += kv[1] * tv[1]; a2 += kv[2] * tv[2]; a3 += kv[3] * tv[3];
+        a0 += kv[4] * tv[4]; a1 += kv[5] * tv[5]; a2 += kv[6] * tv[6];
     }
-    if (tid >= SH::NB - 1) return;
-    const int sj = tid / 14 + 1, cc = tid - 14 * (sj - 1);     // junction x_{3 sj}: right boundary of segment sj-1, left of sj
-    const int sp = sj - 1, nbp = SH::nb(sp), nbo = SH::nb(sj);
-    const double* pp = c.partF + pfoff<SH>(sp) + (sp > 0 ? 14 : 0) + cc;
-    const double* po = c.partF + pfoff<SH>(sj) + cc;
-    double a = pp[0] + pp[nbp], b = po[0] + po[nbo];
-    a += (sp == 0) ? (pp[2 * nbp] + pp[3 * nbp]) : pp[2 * nbp];
-    b += (sj == 5) ? (po[2 * nbo] + po[3 * nbo]) : po[2 * nbo];
-    c.rB[tid] = c.rhs[L::sepidx(tid)] - (a + b);
+    ts.acc = (a0 + a1) + (a2 + a3);
+    // the two dot products of r_B[p] = rhs_p + (A^T w)_p - (F^T rhs_I)_p arrive as 32 partial sums each (phase A: a_rhs_p, phase B:
+    // b_w_p); two threads of warps that idle in this interval add them up, phase C combines them while it loads r_B
+    if (tid == 10 * 32) c.sc[0] = tree32(c.psum);
+    if (tid == 11 * 32) c.sc[1] = tree32(c.psum + 32);
+}
+// (F^T rhs_I)_p = sum_i F[i,p] rhs_i as 32 strided partial sums (phase B, the warp with the fewest W rows)
+template <class SH>
+MPCB_DEV void b_w_p(ACtx<SH>& c, int tid) {
+    if ((tid >> 5) != 15) return;
+    const double* p = c.fpc + (tid & 31);
+    const double* q = c.rhs + (tid & 31);
+    double a0 = p[0] * q[0], a1 = p[32] * q[32], a2 = p[64] * q[64], a3 = p[96] * q[96];
+    a0 += p[128] * q[128]; a1 += p[160] * q[160]; a2 += p[192] * q[192]; a3 += p[224] * q[224];
+    a0 += p[256] * q[256]; a1 += p[288] * q[288]; a2 += p[320] * q[320]; a3 += p[352] * q[352];
+    a0 += p[384] * q[384];
+    c.psum[32 + (tid & 31)] = (a0 + a1) + (a2 + a3);
 }
 // ---- phase C: x~_B = C^-1 r_B, 4 lanes per row ------------------------------------------------------------------------
 template <class SH>
@@ -546,7 +591,12 @@ MPCB_DEV void c_separator(ACtx<SH>& c, ATS<SH>& ts, int tid) {
         const double* rb = c.rB + (tid & 3);
         double rv[18];                                   // read while the tensor-memory loads are in flight
         MPCB_UNROLL
-        for (int jj = 0; jj < 18; jj++) rv[jj] = rb[4 * jj];
+        for (int jj = 0; jj < 17; jj++) rv[jj] = rb[4 * jj];
+        {   // columns 68..71: r_B[p] (column 70) is formed here from its three pieces; 71 is a pad
+            const double rp = (c.rhs[L::IP] + c.sc[0]) - c.sc[1];
+            const int l = tid & 3;
+            rv[17] = l == 2 ? rp : (l < 2 ? rb[68] : 0.0);
+        }
         tm_wait(c0, c1, c2);
         MPCB_UNROLL
         for (int jj = 0; jj < 8; jj += 4) {
@@ -716,6 +766,22 @@ MPCB_DEV void a_finish(ACtx<SH>& c, ATS<SH>& ts, int tid, int max_iter) {
 #define MPCB_WSTAMP(slot)
 #endif
 
+// host emulation of wreduce (same association of the sums as the shuffle network of the device)
+#ifdef MPCB_EMUL
+#define MPCB_WREDUCE_EMUL()                                                                                                     \
+    {                                                                                                                           \
+        const WRole r_ = wrole<SH>(tid);                                                                                        \
+        const int q_ = r_.q, b2_ = (q_ >> 2) & 1, b1_ = (q_ >> 1) & 1, b0_ = q_ & 1;                                            \
+        const int rl_ = r_.kind == 1 ? 4 * b2_ + 2 * b1_ + b0_ : 2 * b2_ + b1_;                                                 \
+        auto P_ = [&](int x) { return tsv[(tid & ~7) | x].pv[rl_]; };                                                           \
+        auto S1_ = [&](int x) { return P_(x) + P_(x ^ 4); };                                                                    \
+        auto S2_ = [&](int x) { return S1_(x) + S1_(x ^ 2); };                                                                  \
+        ts.acc = S2_(q_) + S2_(q_ ^ 1);                                                                                         \
+    }
+#else
+#define MPCB_WREDUCE_EMUL()
+#endif
+
 // One QP: load the block, iterate, store the result.
 template <class SH>
 MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
@@ -733,24 +799,31 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
         MPCB_APHASE_NS(a_rhs(c, ts, tid));
         MPCB_APHASE({ a_rhs_p(c, tid); MPCB_WSTAMP(0) });
         MPCB_PROF(1)
-        MPCB_APHASE({ b_ft(c, ts, tid); MPCB_WSTAMP(1) });
+        // t = W rhs_I, published in the x~ slots of the interior variables (phase D overwrites them with x~_I = t - F x~_B)
+        MPCB_APHASE_NS(b_w(c, ts, tid));
+        MPCB_APHASE({
+            MPCB_WREDUCE_EMUL()
+            const WRole r = wrole<SH>(tid);
+            ts.t = ts.acc;
+            if (r.valid && r.half == 0) c.xt[r.out] = ts.t;
+            b_w_p(c, tid);
+            MPCB_WSTAMP(1)
+        });
         MPCB_PROF(2)
-        MPCB_APHASE({ b_seprhs(c, tid); MPCB_WSTAMP(2) });
+        MPCB_APHASE_NS(b_sbi(c, ts, tid));
+        MPCB_APHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
+        MPCB_APHASE({
+            const double s4 = ts.acc2 + MPCB_PEER(acc2, 2);
+            if (tid < 4 * (SH::NB - 1) && (tid & 3) == 0) c.rB[tid >> 2] = c.rhs[L::sepidx(tid >> 2)] - s4;
+            MPCB_WSTAMP(2)
+        });
         MPCB_PROF(3)
-        // t = W rhs_I only reads rhs and is not needed before phase D.  It runs in the separator-solve interval, after that
-        // interval's own short critical chain (18 multiply-adds on 288 threads, two shuffles, the x~_B store): there it costs
-        // ~610 cycles per iteration; next to the separator rhs it cost ~910, next to F^T rhs_I ~935 (profiles/r1z_*)
         MPCB_APHASE_NS(c_separator(c, ts, tid));
         MPCB_APHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
-        MPCB_APHASE_NS({
+        MPCB_APHASE({
             const double s4 = ts.acc2 + MPCB_PEER(acc2, 2);
             const int cu = L::cunit(tid);
             if (cu >= 0 && (cu & 3) == 0) c.xt[L::sepidx(cu >> 2)] = s4;
-        });
-        MPCB_APHASE_NS(b_w(c, ts, tid));
-        MPCB_APHASE({
-            const double o = MPCB_PEER(acc, 1);
-            ts.t = wrole<SH>(tid).paired ? ts.acc + o : ts.acc;
             MPCB_WSTAMP(3)
         });
         MPCB_PROF(4)

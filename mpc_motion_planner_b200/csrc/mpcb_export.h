@@ -28,20 +28,16 @@ MPCB_DEV void exp_w(const Ctx<SH>& c, int tid, double* qb) {
     typedef AL<SH> L;
     const WRole r = wrole<SH>(tid);
     const double* Wn = c.W + SH::woff(r.seg);
-    for (int e = 0; e < L::WREG; e++) {
-        const int col = wcol<SH>(r, e);
-        qb[L::G_WREG + e * NT + tid] = col >= 0 ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
-    }
+    int row, col;
+    for (int e = 0; e < L::WREG; e++)
+        qb[L::G_WREG + e * NT + tid] = wslot<SH>(r, tid, e, row, col) ? -sym_packed<SH>(Wn, row, col) : 0.0;
     double* tm = qb + L::G_TM + tid;
-    const int nov = tid < 128 ? 0 : (tid < 352 ? 17 : 4);
-    for (int e = 0; e < nov; e++) {
-        const int col = wcol<SH>(r, 32 + e);
-        tm[(L::tm_wov(tid) + e) * NT] = col >= 0 ? -sym_packed<SH>(Wn, r.row, col) : 0.0;
-    }
+    const int nov = 16 * L::wchunks(r.kind);           // overflow slots behind the register part, whole 16-slot chunks
+    for (int e = 0; e < nov; e++)
+        tm[(L::tm_wov(tid) + e) * NT] = wslot<SH>(r, tid, L::WREG + e, row, col) ? -sym_packed<SH>(Wn, row, col) : 0.0;
 }
 // F_s (row-major i*nb + col in the factorisation) -> per-thread pieces in the TMEM strips: the row (or half row) the
-// thread multiplies in phase D, the column chunk it multiplies in phase B1; C^-1 -> 4 units per row; the inequality
-// Jacobian stays in the shared-memory image
+// thread multiplies in phase D; C^-1 -> 4 units per row; the inequality Jacobian stays in the shared-memory image
 template <class SH>
 MPCB_DEV void exp_fc(const Ctx<SH>& c, int tid, double* qb) {
     typedef AL<SH> L;
@@ -59,12 +55,6 @@ MPCB_DEV void exp_fc(const Ctx<SH>& c, int tid, double* qb) {
         } else {
             for (int j = 0; j < 29; j++) tm[(so + j) * NT] = r.valid ? Fs[j] : 0.0;
         }
-    }
-    {
-        const FRole f = frole<SH>(tid);
-        const int so = L::tm_ft(tid);
-        for (int i = 0; i < 18; i++)
-            tm[(so + i) * NT] = (f.unit >= 0 && i < f.len) ? c.F[SH::foff(f.seg) + (f.r0 + i) * SH::nb(f.seg) + f.col] : 0.0;
     }
     if (tid < 128 || tid >= 352) {
         const int cu = L::cunit(tid), so = L::tm_c(tid);
@@ -121,6 +111,29 @@ MPCB_DEV void exp_vec(const Ctx<SH>& c, const TS<SH>& ts, int tid, double* qb) {
         img[L::I_FPC + tid] = fp;
     }
     if (tid < 24) img[L::I_DT + tid] = (tid < 16) ? c.cheb->D[tid >> 2][tid & 3] : (tid == 16 ? c.scal[SC_MTP] : 0.0);
+}
+// BEFORE the sweeps the F area still holds S_IB (the assembled KKT entries between interior and separator variables): the
+// sparse rows S_BI the ADMM kernel uses for part = S_BI t (mpcb_admm.h, sbi_cand) go out here.
+template <class SH>
+MPCB_DEV void exp_sbi(const Ctx<SH>& c, int tid, double* qb) {
+    typedef AL<SH> L;
+    double* img = qb + L::G_IMG;
+    if (tid < L::SBI_T) {
+        const int b = tid >> 2, q = tid & 3;
+        for (int t = 0; t < L::SBI_E; t++) {
+            double v = 0.0;
+            int seg, k, comp;
+            if (b < SH::NB - 1 && sbi_cand<SH>(b, q + 4 * t, seg, k, comp)) {
+                const int l = SH::aug_index(seg, k, comp), nb = SH::nb(seg);       // interior row of the candidate in its segment
+                v = c.F[SH::foff(seg) + l * nb + sbi_col<SH>(b, seg)];
+            }
+            img[L::I_SBI + L::SBI_T * t + tid] = v;
+        }
+    }
+}
+template <class SH>
+MPCB_DEV void export_pre(MPCB_DRIVER_PARAMS(SH), double* qb) {
+    MPCB_PHASE(exp_sbi(c, tid, qb));
 }
 template <class SH>
 MPCB_DEV void export_qp(MPCB_DRIVER_PARAMS(SH), double* qb) {

@@ -133,7 +133,7 @@ admm_kernel(const __grid_constant__ KernelConst kc, const int n, int* __restrict
     tm_fence_after();
     const uint32_t tmem_base = s_tmem;
     {
-        const int w0 = ptid >> 5, w1 = w0 + ANT / 32;      // logical warps; both sit in lane quadrant w0 % 4
+        const int w0 = ptid >> 5, w1 = (w0 + ANT / 32) & 15;      // logical warps; both sit in lane quadrant w0 % 4 (ts1 is unused when ANT == NT)
         const uint32_t lanes = (uint32_t)(32 * (w0 & 3)) << 16;
         ts0.tmaddr = tmem_base + lanes + 2 * tm_warp_base(w0);
         ts1.tmaddr = tmem_base + lanes + 2 * tm_warp_base(w1);

@@ -293,8 +293,9 @@ MPCB_DEV void fac_c_assemble(Ctx<SH>& c, int tid) {
         c.C[i * (i + 1) / 2 + j] = v;
     }
 }
+// KKT assembly: S block-wise into W (S_II, packed lower), F (S_IB, row-major) and BB (S_BB contributions)
 template <class SH>
-MPCB_DEV void factorise(MPCB_DRIVER_PARAMS(SH)) {
+MPCB_DEV void fac_assemble(MPCB_DRIVER_PARAMS(SH)) {
     MPCB_PROF_DECL
     MPCB_PHASE(fac_zero(c, tid));
     MPCB_PHASE(fac_diag(c, ts, tid));
@@ -302,6 +303,11 @@ MPCB_DEV void factorise(MPCB_DRIVER_PARAMS(SH)) {
         for (int cc = 0; cc < 14; cc++) MPCB_PHASE(fac_eq_row(c, tid, j, cc));
     for (int jn = 0; jn <= SH::PO; jn++) MPCB_PHASE(fac_ineq_node(c, tid, jn));
     MPCB_PROF(18)
+}
+// sweeps: interiors, then the separator Schur complement
+template <class SH>
+MPCB_DEV void fac_sweeps(MPCB_DRIVER_PARAMS(SH)) {
+    MPCB_PROF_DECL
     constexpr int PAR = Sweep<SH>::PAR;
     for (int first = 0; first < SH::NS; first += PAR) sweep_round<SH>(MPCB_DRIVER_ARGS, first, SH::NS - first < PAR ? SH::NS - first : PAR, Sweep<SH>::SLOT_I);
     MPCB_PROF(19)
@@ -309,6 +315,11 @@ MPCB_DEV void factorise(MPCB_DRIVER_PARAMS(SH)) {
     sweep_round<SH>(MPCB_DRIVER_ARGS, SH::NS, 1, Sweep<SH>::SLOT_C);
     MPCB_PROF(20)
     // W now holds -S_II^-1 (packed lower, per segment), F = S_II^-1 S_IB, C = -(Schur complement)^-1
+}
+template <class SH>
+MPCB_DEV void factorise(MPCB_DRIVER_PARAMS(SH)) {
+    fac_assemble<SH>(MPCB_DRIVER_ARGS);
+    fac_sweeps<SH>(MPCB_DRIVER_ARGS);
 }
 
 }  // namespace mpcb

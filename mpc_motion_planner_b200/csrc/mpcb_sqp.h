@@ -168,7 +168,9 @@ MPCB_DEV void stage_linfac(MPCB_DRIVER_PARAMS(SH), const Problem& pb, double* qb
     MPCB_PHASE(sqp_load_a(c, tid, pb));
     linearise<SH>(MPCB_DRIVER_ARGS);
     MPCB_PROF(17)
-    factorise<SH>(MPCB_DRIVER_ARGS);
+    fac_assemble<SH>(MPCB_DRIVER_ARGS);
+    export_pre<SH>(MPCB_DRIVER_ARGS, qb);          // S_BI and the row of p, before the sweeps turn S_IB into F
+    fac_sweeps<SH>(MPCB_DRIVER_ARGS);
     MPCB_PROF(25)
     export_qp<SH>(MPCB_DRIVER_ARGS, qb);
     MPCB_PROF(21)

@@ -130,10 +130,12 @@ int emul_kkt_apply(const mpcb_settings* st, const mpcb_limits* lim, const double
         if (L::decode(i, k, comp)) c.rhs[i] = rhs[ext_index<SH>(k, comp)];
     }
     c.sc[0] = 0;        // no A^T w gather in this test: rhs is given directly
-    MPCB_PHASE(b_ft(c, ts, tid));
     MPCB_PHASE_NS(b_w(c, ts, tid));
-    MPCB_PHASE_NS(b_seprhs(c, tid));
-    MPCB_PHASE({ const double o = MPCB_PEER(acc, 1); ts.t = wrole<SH>(tid).paired ? ts.acc + o : ts.acc; });
+    MPCB_PHASE({ MPCB_WREDUCE_EMUL() const WRole r = wrole<SH>(tid); ts.t = ts.acc; if (r.valid && r.half == 0) c.xt[r.out] = ts.t; b_w_p(c, tid); });
+    for (int j = 0; j < 32; j++) c.psum[j] = 0;        // no A^T w gather in this test
+    MPCB_PHASE_NS(b_sbi(c, ts, tid));
+    MPCB_PHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
+    MPCB_PHASE({ const double s4 = ts.acc2 + MPCB_PEER(acc2, 2); if (tid < 4 * (SH::NB - 1) && (tid & 3) == 0) c.rB[tid >> 2] = c.rhs[L::sepidx(tid >> 2)] - s4; });
     MPCB_PHASE_NS(c_separator(c, ts, tid));
     MPCB_PHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
     MPCB_PHASE({ const double s4 = ts.acc2 + MPCB_PEER(acc2, 2); const int cu = L::cunit(tid); if (cu >= 0 && (cu & 3) == 0) c.xt[L::sepidx(cu >> 2)] = s4; });

@@ -38,3 +38,12 @@ build/offline_trajectory: examples/offline_trajectory.cpp include/motion_planner
 	$(CXX) -O2 -std=c++17 -Wall -Iinclude $< -o $@ -L$(dir $(OUT)) -lmpcb -Wl,-rpath,'$$ORIGIN/../$(dir $(OUT))'
 build/mpc_benchmark: examples/benchmark.cpp include/motion_planner.hpp $(OUT)
 	$(CXX) -O2 -std=c++17 -Wall -Iinclude $< -o $@ -L$(dir $(OUT)) -lmpcb -Wl,-rpath,'$$ORIGIN/../$(dir $(OUT))'
+
+# The reference's own example mains, compiled UNCHANGED from /root/reference (never copied) against shim/ (a minimal Eigen / pinocchio
+# surface + an Eigen-typed MotionPlanner adapter over include/motion_planner.hpp).  Only where the reference tree is mounted.
+REF ?= /root/reference
+examples-unchanged: build/ref_offline_trajectory build/ref_mpc_benchmark
+build/ref_offline_trajectory: $(REF)/examples/offline_trajectory.cpp shim/motionPlanner.hpp shim/Eigen/Dense include/motion_planner.hpp $(OUT)
+	$(CXX) -O2 -std=c++17 -Ishim -Iinclude $< -o $@ -L$(dir $(OUT)) -lmpcb -Wl,-rpath,'$$ORIGIN/../$(dir $(OUT))'
+build/ref_mpc_benchmark: $(REF)/examples/benchmark.cpp shim/motionPlanner.hpp shim/Eigen/Dense include/motion_planner.hpp $(OUT)
+	$(CXX) -O2 -std=c++17 -Ishim -Iinclude $< -o $@ -L$(dir $(OUT)) -lmpcb -Wl,-rpath,'$$ORIGIN/../$(dir $(OUT))'

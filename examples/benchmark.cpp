@@ -36,6 +36,10 @@ int main(int argc, char** argv) {
     std::vector<mpcb_account> acc(n);
     if (mpcb_sample_batch(planner.handle(), n, sx.data(), su.data(), sT.data(), xT.data(), nPoints, nullptr, acc.data(), MPCB_MEM_HOST, nullptr) != MPCB_OK)
         throw std::runtime_error(mpcb_last_error(planner.handle()));
+    // the warm-start ("Ruckig") half of the accounting, benchmark.cpp:72-114, on the device too (sample_profile_kernel)
+    std::vector<mpcb_account> acc_rk(n);
+    if (mpcb_sample_profile_batch(planner.handle(), n, x0.data(), xT.data(), nPoints, nullptr, acc_rk.data(), nullptr, MPCB_MEM_HOST, nullptr) != MPCB_OK)
+        throw std::runtime_error(mpcb_last_error(planner.handle()));
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 
     std::ofstream f(out, std::ios_base::app);
@@ -44,42 +48,17 @@ int main(int argc, char** argv) {
     int fails[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     double meanT = 0;
     for (int i = 0; i < n; i++) {
-        Vec7 q0, v0, q1, v1;
-        for (int j = 0; j < 7; j++) { q0[j] = x0[14 * i + j]; v0[j] = x0[14 * i + 7 + j]; q1[j] = xT[14 * i + j]; v1[j] = xT[14 * i + 7 + j]; }
-        // warm-start ("ruckig") half on the host: benchmark.cpp:72-114
-        planner.set_current_state(q0, v0);
-        planner.set_target_state(q1, v1);
-        planner.warm_start_profile();
-        Traj<1> time; Traj<7> pos, vel, a, tau;
-        planner.get_ruckig_trajectory<nPoints>(time, pos, vel, a, tau);
-        int flags_rk[4] = {1, 1, 1, 1};
-        const double dT = time(0, nPoints) / nPoints;
-        for (int p = 0; p <= nPoints; p++) {
-            if (p >= 1)
-                for (int j = 0; j < 7; j++)
-                    if (std::fabs((a(j, p) - a(j, p - 1)) / dT) > 10 * planner.robot.max_jerk[j]) flags_rk[0] = 0;
-            const Vec6 tv = planner.robot.forward_velocities(pos.col(p), vel.col(p));
-            if (tv.head<3>().norm() > planner.robot.max_linear_velocity) flags_rk[1] = 0;
-            if (tv.tail<3>().norm() > planner.robot.max_angular_velocity) flags_rk[2] = 0;
-            if (planner.robot.tool_height(pos.col(p)) < 0) flags_rk[3] = 0;
-        }
-        for (int r = 0; r < 7; r++) f << pos.rowMin(r) << " ";
-        for (int r = 0; r < 7; r++) f << vel.rowMin(r) << " ";
-        for (int r = 0; r < 7; r++) f << a.rowMin(r) << " ";
-        for (int r = 0; r < 7; r++) f << tau.rowMin(r) << " ";
-        for (int r = 0; r < 7; r++) f << pos.rowMax(r) << " ";
-        for (int r = 0; r < 7; r++) f << vel.rowMax(r) << " ";
-        for (int r = 0; r < 7; r++) f << a.rowMax(r) << " ";
-        for (int r = 0; r < 7; r++) f << tau.rowMax(r) << " ";
+        // row format of benchmark.cpp:169-193: min / max of the 28 signals (warm start, MPC), final-state errors, 8 flags, target
+        for (int r = 0; r < 28; r++) f << acc_rk[i].mins[r] << " ";
+        for (int r = 0; r < 28; r++) f << acc_rk[i].maxs[r] << " ";
         for (int r = 0; r < 28; r++) f << acc[i].mins[r] << " ";
         for (int r = 0; r < 28; r++) f << acc[i].maxs[r] << " ";
-        for (int j = 0; j < 7; j++) f << pos(j, nPoints) - q1[j] << " ";
-        for (int j = 0; j < 7; j++) f << vel(j, nPoints) - v1[j] << " ";
+        for (int j = 0; j < 14; j++) f << acc_rk[i].final_err[j] << " ";
         for (int j = 0; j < 14; j++) f << acc[i].final_err[j] << " ";
-        for (int k = 0; k < 4; k++) { f << flags_rk[k] << " "; fails[k] += !flags_rk[k]; }
+        for (int k = 0; k < 4; k++) { f << acc_rk[i].flags[k] << " "; fails[k] += !acc_rk[i].flags[k]; }
         for (int k = 0; k < 4; k++) { f << acc[i].flags[k] << " "; fails[4 + k] += !acc[i].flags[k]; }
-        for (int j = 0; j < 7; j++) f << q1[j] << " ";
-        for (int j = 0; j < 7; j++) f << v1[j] << (j < 6 ? " " : "\n");
+        for (int j = 0; j < 7; j++) f << xT[14 * i + j] << " ";
+        for (int j = 0; j < 7; j++) f << xT[14 * i + 7 + j] << (j < 6 ? " " : "\n");
         meanT += sT[i];
     }
     std::cout << n << " trajectories solved + sampled in " << secs << " s (" << n / secs << " OCP/s end to end); mean final time " << meanT / n << " s\n"

@@ -21,6 +21,12 @@
 
 #include "mpcb.h"
 
+// The class is called MotionPlanner, as in the reference.  shim/motionPlanner.hpp (the Eigen-typed adapter that lets the
+// reference's own mains compile unchanged) includes this header under another class name and wraps it.
+#ifndef MPCB_PLANNER_CLASS
+#define MPCB_PLANNER_CLASS MotionPlanner
+#endif
+
 #define NDOF 7
 
 namespace mpcb {
@@ -103,7 +109,7 @@ class PandaWrapper {
 
 }  // namespace mpcb
 
-class MotionPlanner {
+class MPCB_PLANNER_CLASS {
   public:
     typedef mpcb::Vec7 Vec7;
     typedef mpcb::Vec<14> State;
@@ -114,7 +120,7 @@ class MotionPlanner {
     double margin_position_, margin_velocity_, margin_acceleration_, margin_torque_, margin_jerk_;
     mpcb_stats last_stats;                           // polympc's info() of the last solve
 
-    explicit MotionPlanner(const std::string& urdf_path, int device = 0, unsigned long long seed = 0) : robot(urdf_path), seed_(seed) {
+    explicit MPCB_PLANNER_CLASS(const std::string& urdf_path, int device = 0, unsigned long long seed = 0) : robot(urdf_path), seed_(seed) {
         mpcb_default_settings(&settings_);           // motionPlanner.cpp:15-20
         mpcb_default_limits(&limits_);
         const int rc = mpcb_create(&settings_, device, &h_);
@@ -130,9 +136,9 @@ class MotionPlanner {
         set_current_state(mid, Vec7::Zero());
         set_constraint_margins(1.0, 1.0, 1.0, 1.0, 1.0);                                             // motionPlanner.cpp:24
     }
-    ~MotionPlanner() { mpcb_destroy(h_); }
-    MotionPlanner(const MotionPlanner&) = delete;
-    MotionPlanner& operator=(const MotionPlanner&) = delete;
+    ~MPCB_PLANNER_CLASS() { mpcb_destroy(h_); }
+    MPCB_PLANNER_CLASS(const MPCB_PLANNER_CLASS&) = delete;
+    MPCB_PLANNER_CLASS& operator=(const MPCB_PLANNER_CLASS&) = delete;
 
     // motionPlanner.cpp:27-39: final state box = target +- eps
     // The acceleration argument only feeds Ruckig in the reference (motionPlanner.cpp:36-38); the profile generator here starts and

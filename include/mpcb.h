@@ -197,6 +197,13 @@ int mpcb_guess_batch(const mpcb_settings* s, const mpcb_limits* lim, int n, cons
 int mpcb_guess_batch_gpu(mpcb_handle* h, int n, const double* x0, const double* xT, double* guess_x, double* guess_u, double* guess_T,
                          int mem, void* cuda_stream);
 
+/* The warm-start ("Ruckig") half of the benchmark on the device: get_ruckig_trajectory<npts> (motionPlanner.hpp:73-96) of the jerk-limited
+ * profile from x0 to xT under the handle's limits, with the per-trajectory checks of examples/benchmark.cpp:72-114 (same flags, extrema and
+ * final-state error as mpcb_sample_batch computes for the MPC half).  traj n x (npts+1) x 29, acc n, T_out n (profile durations); each may
+ * be NULL.  sample_profile_kernel: one CTA per problem, the profile by the routines the warm start uses. */
+int mpcb_sample_profile_batch(mpcb_handle* h, int n, const double* x0, const double* xT, int npts, double* traj, mpcb_account* acc,
+                              double* T_out, int mem, void* cuda_stream);
+
 /* mpcb_generate_problems on the device of handle `h` with its current limits (gen_problems_kernel, one problem per thread): problem i of
  * the call draws from stream (seed, first + i), so a rank generates its shard [first, first + n) of a batch in place.  Same routines as
  * the host version; results agree to rounding (device sin/cos and contracted multiply-adds). */

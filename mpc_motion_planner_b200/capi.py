@@ -271,6 +271,16 @@ class Solver:
         self._check(self.L.mpcb_debug_node_constraints(self.h, C.c_int(n), _p(qva), _p(gv), _p(gj), _p(Jg)), "mpcb_debug_node_constraints")
         return gv, gj, Jg
 
+    def sample_profile(self, x0, xT, npts=200, want_traj=True, want_acc=True):
+        """The warm-start profile sampled on the device with the benchmark's checks: (traj (n, npts+1, 29), account, durations)."""
+        x0 = _d(np.atleast_2d(x0)); xT = _d(np.atleast_2d(xT)); n = x0.shape[0]
+        traj = np.zeros((n, npts + 1, 29)) if want_traj else None
+        acc = np.zeros(n, dtype=ACCOUNT_DTYPE) if want_acc else None
+        T = np.zeros(n)
+        rc = self.L.mpcb_sample_profile_batch(self.h, C.c_int(n), _p(x0), _p(xT), C.c_int(npts), _p(traj), _p(acc), _p(T), C.c_int(MEM_HOST), None)
+        self._check(rc, "mpcb_sample_profile_batch")
+        return traj, acc, T
+
     def last_solve_ms(self):
         return self.L.mpcb_last_solve_ms(self.h)
 

@@ -339,6 +339,57 @@ int mpcb_sample_batch(mpcb_handle* h, int n, const double* sol_x, const double* 
     return MPCB_OK;
 }
 
+static int fill_otg_const(mpcb_handle* h, OtgConst* oc) {
+    oc->N = mpcb_num_nodes(&h->st);
+    if (oc->N > 64 || mpcb_time_nodes(&h->st, oc->tn) != MPCB_OK) { h->err = "unsupported number of nodes"; return MPCB_ERR_UNSUPPORTED; }
+    for (int d = 0; d < 7; d++) {
+        oc->vl[d] = h->lim.margins[1] * h->lim.vmax[d]; oc->al[d] = h->lim.margins[2] * h->lim.amax[d]; oc->jl[d] = h->lim.margins[4] * h->lim.jmax[d];
+    }
+    oc->p_ub = h->lim.p_ub;
+    return MPCB_OK;
+}
+
+int mpcb_sample_profile_batch(mpcb_handle* h, int n, const double* x0, const double* xT, int npts, double* traj, mpcb_account* acc, double* T_out,
+                              int mem, void* stream_) {
+    if (!h) return MPCB_ERR_BAD_ARG;
+    if (n < 0 || npts < 1 || npts > 1000 || (n > 0 && (!x0 || !xT))) { h->err = "bad argument"; return MPCB_ERR_BAD_ARG; }
+    if (mem != MPCB_MEM_HOST && mem != MPCB_MEM_DEVICE) { h->err = "mem must be MPCB_MEM_HOST or MPCB_MEM_DEVICE"; return MPCB_ERR_BAD_ARG; }
+    if (n == 0 || (!traj && !acc && !T_out)) return MPCB_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CK(cudaSetDevice(h->device));
+    CK(handle_enter(h, stream));
+    OtgConst oc;
+    { int rc = fill_otg_const(h, &oc); if (rc) return rc; }
+    const size_t b14 = sizeof(double) * 14 * n, btraj = sizeof(double) * 29 * (npts + 1) * n, bacc = sizeof(mpcb_account) * n, bT = sizeof(double) * n;
+    const double *dx0 = x0, *dxT = xT;
+    double *dtraj = traj, *dT = T_out;
+    mpcb_account* dacc = acc;
+    if (mem == MPCB_MEM_HOST) {
+        int rc = ensure_stage(h, 2 * al(b14) + (traj ? al(btraj) : 0) + (acc ? al(bacc) : 0) + (T_out ? al(bT) : 0));
+        if (rc) return rc;
+        char* p = (char*)h->d_stage;
+        auto take = [&](size_t b) { char* r = p; p += al(b); return r; };
+        double* a = (double*)take(b14); double* b = (double*)take(b14);
+        CK(cudaMemcpyAsync(a, x0, b14, cudaMemcpyHostToDevice, stream));
+        CK(cudaMemcpyAsync(b, xT, b14, cudaMemcpyHostToDevice, stream));
+        dx0 = a; dxT = b;
+        if (traj) dtraj = (double*)take(btraj);
+        if (acc) dacc = (mpcb_account*)take(bacc);
+        if (T_out) dT = (double*)take(bT);
+    }
+    const int grid = n < 8 * h->sm_count ? n : 8 * h->sm_count;
+    CK(launch_sample_profile(oc, h->kc, n, dx0, dxT, npts, dtraj, dacc, dT, grid, stream));
+    h->launches += 1;
+    if (mem == MPCB_MEM_HOST) {
+        if (traj) CK(cudaMemcpyAsync(traj, dtraj, btraj, cudaMemcpyDeviceToHost, stream));
+        if (acc) CK(cudaMemcpyAsync(acc, dacc, bacc, cudaMemcpyDeviceToHost, stream));
+        if (T_out) CK(cudaMemcpyAsync(T_out, dT, bT, cudaMemcpyDeviceToHost, stream));
+        CK(cudaStreamSynchronize(stream));
+    }
+    CK(handle_leave(h, stream));
+    return MPCB_OK;
+}
+
 int mpcb_guess_batch_gpu(mpcb_handle* h, int n, const double* x0, const double* xT, double* gx, double* gu, double* gT, int mem, void* stream_) {
     if (!h) return MPCB_ERR_BAD_ARG;
     if (n < 0 || (n > 0 && (!x0 || !xT || !gx || !gu || !gT))) { h->err = "bad argument"; return MPCB_ERR_BAD_ARG; }
@@ -348,12 +399,7 @@ int mpcb_guess_batch_gpu(mpcb_handle* h, int n, const double* x0, const double* 
     CK(cudaSetDevice(h->device));
     CK(handle_enter(h, stream));
     OtgConst oc;
-    oc.N = mpcb_num_nodes(&h->st);
-    if (oc.N > 64 || mpcb_time_nodes(&h->st, oc.tn) != MPCB_OK) { h->err = "unsupported number of nodes"; return MPCB_ERR_UNSUPPORTED; }
-    for (int d = 0; d < 7; d++) {
-        oc.vl[d] = h->lim.margins[1] * h->lim.vmax[d]; oc.al[d] = h->lim.margins[2] * h->lim.amax[d]; oc.jl[d] = h->lim.margins[4] * h->lim.jmax[d];
-    }
-    oc.p_ub = h->lim.p_ub;
+    { int rc = fill_otg_const(h, &oc); if (rc) return rc; }
     const int N = oc.N;
     const size_t b14 = sizeof(double) * 14 * n, bgx = sizeof(double) * 14 * N * n, bgu = sizeof(double) * 7 * N * n, bT = sizeof(double) * n;
     const double *dx0 = x0, *dxT = xT;

@@ -87,6 +87,8 @@ struct Sweep {
     static constexpr int SLOT_I = tiles(SH::AUGMAX), SLOT_C = tiles(SH::NB);           // threads per interior matrix / for the separator
     static constexpr int PAR0 = SH::NT / SLOT_I;
     static constexpr int PAR = PAR0 > SH::NS ? SH::NS : (PAR0 > 6 ? 6 : PAR0);          // interior matrices swept per round
+    // scratch of the blocked sweep per matrix: raw panel M x 5 | scaled panel M x 5 | inverse of the diagonal tile (25)
+    static constexpr int PANEL = 2 * TILE * ((MAXM + TILE - 1) / TILE * TILE) + 32;
     static_assert(SLOT_I <= SH::NT && SLOT_C <= SH::NT && PAR >= 1, "sweep tiling: one thread per 5 x 5 tile of the largest matrix");
 };
 
@@ -95,7 +97,9 @@ struct Layout {   // offsets in doubles into the dynamic shared-memory block
     // The matrix area (W | F | C | BB) sits in shared memory when it fits (the base shape); for the larger collocation shapes
     // it lives in a per-CTA block of global memory (Ctx::bind gets the pointer) and only vectors + Jacobians stay on chip.
     static constexpr bool GMAT = (SH::MATSIZE + SH::BBSIZE) > 22000;
-    static constexpr int MATDOUBLES = SH::MATSIZE + SH::BBSIZE + SH::FULLSIZE;     // per-CTA global block: packed factors + full copies
+    static constexpr int MATDOUBLES = SH::MATSIZE + SH::BBSIZE + SH::FULLSIZE;     // packed factors + full copies (GMAT shapes)
+    // per-CTA block in global memory: the matrices of the GMAT shapes (a token block otherwise)
+    static constexpr int CTA_BLOCK = GMAT ? MATDOUBLES : 8;
     static constexpr int MAT = 0;                                  // W | F | C   (also: QP result)
     static constexpr int W = MAT, F = W + SH::WSIZE, C = F + SH::FSIZE;
     static constexpr int BB = MAT + SH::MATSIZE;
@@ -108,7 +112,10 @@ struct Layout {   // offsets in doubles into the dynamic shared-memory block
     static constexpr int PART = PCOL + SH::NEQ;                    // F^T rhs partials
     static constexpr int PSUM = PART + SH::PARTSIZE + 1;           // 2 x 32 partial sums
     static constexpr int COLBUF = (PSUM + 64 + 1) / 2 * 2;         // 2 x PAR published pivot columns
-    static constexpr int LIMS = COLBUF + 2 * Sweep<SH>::PAR * Sweep<SH>::COLS;   // per-joint bounds 5x7 + 5, x0, xT
+    // (shapes whose matrices live in global memory keep the panels of the blocked sweep here too; the base shape parks them in
+    // the matrix area itself, whose content sits in the register tiles while a sweep runs)
+    static constexpr int COLBUF_SIZE = 2 * Sweep<SH>::PAR * Sweep<SH>::COLS + (GMAT ? Sweep<SH>::PAR * Sweep<SH>::PANEL : 0);
+    static constexpr int LIMS = COLBUF + COLBUF_SIZE;   // per-joint bounds 5x7 + 5, x0, xT
     static constexpr int SCAL = LIMS + 72;
     static constexpr int UMAX = SCAL + SC_COUNT;
     static constexpr int ISC = UMAX + UM_COUNT;
@@ -147,10 +154,11 @@ struct Ctx {
     // results of the last QP, aliased onto the matrix area after the ADMM loop
     double* qp_p;                  // step p, kernel order
     double* qp_lam;                // QP multipliers
-    // gmat: this CTA's matrix block in global memory (Layout::MATDOUBLES doubles), used when Layout::GMAT
-    MPCB_HD void bind(double* smem, double* gmat = nullptr) {
+    // block: this CTA's block in global memory (Layout::CTA_BLOCK doubles)
+    MPCB_HD void bind(double* smem, double* block) {
         typedef Layout<SH> L;
         sm = smem;
+        double* gmat = block;
         double* mat = L::GMAT ? gmat : sm + L::MAT;
         W = mat; F = mat + SH::WSIZE; C = F + SH::FSIZE; BB = mat + SH::MATSIZE; Jg = sm + L::JG; w = sm + L::VW; rhs = sm + L::VRHS;
         Wf = L::GMAT ? gmat + SH::MATSIZE + SH::BBSIZE : nullptr; Fc = L::GMAT ? Wf + SH::WFSIZE : nullptr; Cf = L::GMAT ? Fc + SH::FSIZE : nullptr;

@@ -55,7 +55,7 @@ sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, con
     extern __shared__ double smem[];
     const int tid = threadIdx.x;
     Ctx<SH> c;
-    c.bind(smem, Layout<SH>::GMAT ? gmat + (size_t)blockIdx.x * Layout<SH>::MATDOUBLES : nullptr);
+    c.bind(smem, gmat + (size_t)blockIdx.x * Layout<SH>::CTA_BLOCK);
     volatile long long& s_next = *reinterpret_cast<volatile long long*>(c.isc + IS_NEXT);
     c.st = &kc.st;
     c.cheb = &kc.cheb;
@@ -242,15 +242,14 @@ sample_kernel(const __grid_constant__ KernelConst kc, const double* __restrict__
 // a longer T while any joint sits in a blocked interval, then every lane samples its joint at the node times.  The per-joint
 // routines are the ones the host path uses (csrc/mpcb_otg.h), so both paths take the same decisions.
 constexpr int OTG_NT = 128;
-__global__ void __launch_bounds__(OTG_NT)
-otg_guess_kernel(const __grid_constant__ OtgConst oc, const int n, const double* __restrict__ x0, const double* __restrict__ xT,
-                 double* __restrict__ gx, double* __restrict__ gu, double* __restrict__ gT) {
-    const int gt = blockIdx.x * OTG_NT + threadIdx.x, i = gt >> 3, d = gt & 7, lane = threadIdx.x & 31;
-    if (i >= n) return;                                   // whole groups leave together
-    const unsigned gmask = 0xFFu << (lane & 24);
+// The profile of one problem by its group of 8 lanes (lane d < 7 owns joint d): on return every lane knows the common duration T
+// and whether the group fell back to the cubic-Hermite profile; lane d holds the 7 phases (t, j) of its joint otherwise.
+struct OtgLane { double q0, v0, q1, v1, vl, al, T, t[7], j[7]; bool act, fallback; };
+__device__ __forceinline__ void otg_group_profile(const OtgConst& oc, const double* __restrict__ x0, const double* __restrict__ xT, int d, unsigned gmask,
+                                                  OtgLane& L) {
     const bool act = d < 7;
     const int dd = act ? d : 0;
-    const double q0 = x0[(size_t)14 * i + dd], v0 = x0[(size_t)14 * i + 7 + dd], q1 = xT[(size_t)14 * i + dd], v1 = xT[(size_t)14 * i + 7 + dd];
+    const double q0 = x0[dd], v0 = x0[7 + dd], q1 = xT[dd], v1 = xT[7 + dd];
     const double vl = oc.vl[dd], al = oc.al[dd], jl = oc.jl[dd];
     double Tmin = 0, vco = 0;
     bool bad = false;
@@ -278,17 +277,10 @@ otg_guess_kernel(const __grid_constant__ OtgConst oc, const int n, const double*
         fallback = !all || !(T > 0 && T <= oc.p_ub);
         if (!fallback && need) vc = otg::sync_bisect(q1 - q0, v0, v1, al, jl, T, lo, hi);
     }
-    const int N = oc.N;
     if (!fallback) {
         if (act) {
-            double t[7], j[7];
             const otg::Eval e = otg::eval_vc(q1 - q0, v0, v1, vc, al, jl);
-            otg::dof_phases(v0, v1, vc, e.tc, al, jl, t, j);
-            for (int k = 0; k < N; k++) {
-                double q, v, a;
-                otg::dof_at_time(t, j, q0, v0, oc.tn[k] * T, &q, &v, &a);
-                gx[((size_t)i * N + k) * 14 + d] = q; gx[((size_t)i * N + k) * 14 + 7 + d] = v; gu[((size_t)i * N + k) * 7 + d] = a;
-            }
+            otg::dof_phases(v0, v1, vc, e.tc, al, jl, L.t, L.j);
         }
     } else {
         T = 0.05;
@@ -299,14 +291,99 @@ otg_guess_kernel(const __grid_constant__ OtgConst oc, const int n, const double*
             T *= 1.05;
             if (T > oc.p_ub) T = oc.p_ub;
         }
-        if (act)
-            for (int k = 0; k < N; k++) {
-                double q, v, a;
-                otg::hermite_eval(q0, v0, q1, v1, T, oc.tn[k], &q, &v, &a);
-                gx[((size_t)i * N + k) * 14 + d] = q; gx[((size_t)i * N + k) * 14 + 7 + d] = v; gu[((size_t)i * N + k) * 7 + d] = a;
-            }
     }
-    if (d == 0) gT[i] = T;
+    L.q0 = q0; L.v0 = v0; L.q1 = q1; L.v1 = v1; L.vl = vl; L.al = al; L.T = T; L.act = act; L.fallback = fallback;
+}
+// state of the lane's joint at time `time` in [0, T] (profile or fallback)
+__device__ __forceinline__ void otg_lane_at(const OtgLane& L, double time, double* q, double* v, double* a) {
+    if (!L.fallback) otg::dof_at_time(L.t, L.j, L.q0, L.v0, time, q, v, a);
+    else otg::hermite_eval(L.q0, L.v0, L.q1, L.v1, L.T, L.T > 0 ? time / L.T : 0.0, q, v, a);
+}
+
+__global__ void __launch_bounds__(OTG_NT)
+otg_guess_kernel(const __grid_constant__ OtgConst oc, const int n, const double* __restrict__ x0, const double* __restrict__ xT,
+                 double* __restrict__ gx, double* __restrict__ gu, double* __restrict__ gT) {
+    const int gt = blockIdx.x * OTG_NT + threadIdx.x, i = gt >> 3, d = gt & 7, lane = threadIdx.x & 31;
+    if (i >= n) return;                                   // whole groups leave together
+    const unsigned gmask = 0xFFu << (lane & 24);
+    OtgLane L;
+    otg_group_profile(oc, x0 + (size_t)14 * i, xT + (size_t)14 * i, d, gmask, L);
+    const int N = oc.N;
+    if (L.act)
+        for (int k = 0; k < N; k++) {
+            double q, v, a;
+            if (!L.fallback) otg::dof_at_time(L.t, L.j, L.q0, L.v0, oc.tn[k] * L.T, &q, &v, &a);
+            else otg::hermite_eval(L.q0, L.v0, L.q1, L.v1, L.T, oc.tn[k], &q, &v, &a);
+            gx[((size_t)i * N + k) * 14 + d] = q; gx[((size_t)i * N + k) * 14 + 7 + d] = v; gu[((size_t)i * N + k) * 7 + d] = a;
+        }
+    if (d == 0) gT[i] = L.T;
+}
+
+// ---- the warm-start ("Ruckig") half of the benchmark: get_ruckig_trajectory<N> + the checks of examples/benchmark.cpp:72-114 ------
+// One CTA per problem: the first 8 lanes build the profile (same routines as the warm start), every joint's samples go to shared
+// memory, then the threads take one sample each: RNEA torque, Cartesian tool velocity, tool height, and the extrema / jerk pass.
+constexpr int PROFILE_NT = 256;
+__global__ void __launch_bounds__(PROFILE_NT)
+sample_profile_kernel(const __grid_constant__ OtgConst oc, const __grid_constant__ KernelConst kc, const int n, const double* __restrict__ x0,
+                      const double* __restrict__ xT, const int npts, double* __restrict__ traj, mpcb_account* __restrict__ acc, double* __restrict__ Tout) {
+    extern __shared__ double rows[];            // (npts+1) x 29
+    __shared__ int flags[4];
+    __shared__ double sT;
+    const int tid = threadIdx.x;
+    for (int ocp = blockIdx.x; ocp < n; ocp += gridDim.x) {
+        if (tid < 4) flags[tid] = 1;
+        if (tid < 8) {
+            OtgLane L;
+            otg_group_profile(oc, x0 + (size_t)14 * ocp, xT + (size_t)14 * ocp, tid, 0xFFu, L);
+            if (tid == 0) sT = L.T;
+            if (L.act)
+                for (int i = 0; i <= npts; i++) {
+                    double q, v, a;
+                    otg_lane_at(L, L.T / npts * i, &q, &v, &a);          // motionPlanner.hpp:77-85
+                    rows[29 * i + 1 + tid] = q; rows[29 * i + 8 + tid] = v; rows[29 * i + 15 + tid] = a;
+                }
+        }
+        __syncthreads();
+        const double T = sT;
+        for (int i = tid; i <= npts; i += PROFILE_NT) {
+            double* row = rows + 29 * i;
+            double q[7], v[7], a[7], g[8];
+            for (int cc = 0; cc < 7; cc++) { q[cc] = row[1 + cc]; v[cc] = row[8 + cc]; a[cc] = row[15 + cc]; }
+            rbd::node_constraints_value(q, v, a, g);        // torque by RNEA (motionPlanner.hpp:91-94)
+            for (int cc = 0; cc < 7; cc++) row[22 + cc] = g[cc];
+            row[0] = T / npts * i;
+            if (acc) {
+                double oR[7][9], op[7][3], J[42], pos[3], tv[6];
+                rbd::fk_world(q, oR, op);
+                rbd::frame_jacobian(oR, op, PANDA(PANDA_TOOL_OFFSET), J, pos);
+                for (int r = 0; r < 6; r++) { double sum = 0; for (int j = 0; j < 7; j++) sum += J[r * 7 + j] * v[j]; tv[r] = sum; }
+                if (sqrt(tv[0] * tv[0] + tv[1] * tv[1] + tv[2] * tv[2]) > 1.7) flags[1] = 0;      // benchmark.cpp:96-103
+                if (sqrt(tv[3] * tv[3] + tv[4] * tv[4] + tv[5] * tv[5]) > 2.5) flags[2] = 0;
+                if (pos[2] < 0) flags[3] = 0;                                                   // benchmark.cpp:108-113
+            }
+        }
+        __syncthreads();
+        if (acc) {
+            const double dT = rows[29 * npts] / npts;       // benchmark.cpp:82
+            for (int i = 1 + tid; i <= npts; i += PROFILE_NT)
+                for (int j = 0; j < 7; j++) {
+                    const double jerk = (rows[29 * i + 15 + j] - rows[29 * (i - 1) + 15 + j]) / dT;
+                    if (fabs(jerk) > 10 * kc.jmax[j]) flags[0] = 0;      // benchmark.cpp:89
+                }
+            if (tid < 28) {
+                double mn = INFINITY, mx = -INFINITY;
+                for (int i = 0; i <= npts; i++) { const double x = rows[29 * i + 1 + tid]; mn = fmin(mn, x); mx = fmax(mx, x); }
+                acc[ocp].mins[tid] = mn; acc[ocp].maxs[tid] = mx;
+            }
+            if (tid < 14) acc[ocp].final_err[tid] = rows[29 * npts + 1 + tid] - xT[(size_t)14 * ocp + tid];
+        }
+        if (traj)
+            for (int e = tid; e < 29 * (npts + 1); e += PROFILE_NT) traj[(size_t)ocp * 29 * (npts + 1) + e] = rows[e];
+        if (Tout && tid == 0) Tout[ocp] = T;
+        __syncthreads();
+        if (acc && tid < 4) acc[ocp].flags[tid] = flags[tid];
+        __syncthreads();
+    }
 }
 
 // ---- problem generator: one problem per thread (the routines of mpcb_gen.h, shared with mpcb_generate_problems) -----------------
@@ -379,7 +456,7 @@ int shape_supported(int po, int ns) { return (po == 3 && (ns == 6 || ns == 12)) 
 cudaError_t shape_info(int po, int ns, ShapeInfo* si) {
     MPCB_FOR_SHAPE(po, ns, {
         si->stage_smem = Layout<SH>::BYTES; si->stage_threads = SH::NT; si->ws_doubles = WS<SH>::STRIDE;
-        si->gmat_doubles = Layout<SH>::GMAT ? (size_t)Layout<SH>::MATDOUBLES : 0;
+        si->gmat_doubles = (size_t)Layout<SH>::CTA_BLOCK;
         si->admm_smem = admm_smem_of<SH>();
     });
     return cudaSuccess;
@@ -429,6 +506,14 @@ cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double*
 cudaError_t launch_otg_guess(const OtgConst& oc, int n, const double* x0, const double* xT, double* gx, double* gu, double* gT, cudaStream_t stream) {
     const long long threads = 8ll * n;
     otg_guess_kernel<<<(unsigned)((threads + OTG_NT - 1) / OTG_NT), OTG_NT, 0, stream>>>(oc, n, x0, xT, gx, gu, gT);
+    return cudaGetLastError();
+}
+cudaError_t launch_sample_profile(const OtgConst& oc, const KernelConst& kc, int n, const double* x0, const double* xT, int npts, double* traj,
+                                  mpcb_account* acc, double* Tout, int grid, cudaStream_t stream) {
+    const size_t smem = (size_t)29 * (npts + 1) * sizeof(double);
+    cudaError_t e = cudaFuncSetAttribute(sample_profile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    sample_profile_kernel<<<grid, PROFILE_NT, smem, stream>>>(oc, kc, n, x0, xT, npts, traj, acc, Tout);
     return cudaGetLastError();
 }
 cudaError_t launch_gen_problems(const mpcb_limits& lim, int kind, unsigned long long seed, unsigned long long first, int n, double* x0, double* xT,

@@ -51,6 +51,9 @@ cudaError_t launch_sample(const KernelConst& kc, const double* sx, const double*
                           double* traj, mpcb_account* acc, int n, int grid, cudaStream_t stream);
 // warm start: jerk-limited synchronised profiles sampled at the node times (8 lanes per problem, one joint per lane)
 cudaError_t launch_otg_guess(const OtgConst& oc, int n, const double* x0, const double* xT, double* gx, double* gu, double* gT, cudaStream_t stream);
+// warm-start profile read-out + benchmark accounting (the Ruckig half of examples/benchmark.cpp:72-114), one CTA per problem
+cudaError_t launch_sample_profile(const OtgConst& oc, const KernelConst& kc, int n, const double* x0, const double* xT, int npts, double* traj,
+                                  mpcb_account* acc, double* Tout, int grid, cudaStream_t stream);
 // problem generator: problem i of the launch draws from stream (seed, first + i)
 cudaError_t launch_gen_problems(const mpcb_limits& lim, int kind, unsigned long long seed, unsigned long long first, int n, double* x0, double* xT,
                                 cudaStream_t stream);

@@ -152,7 +152,14 @@ MPCB_DEV void fac_ineq_node(Ctx<SH>& c, int tid, int jn) {
 // triangle (diagonal tiles are kept full); one thread keeps one tile in registers for all m pivots.  Per pivot the threads
 // that hold the pivot column publish it (and 1/pivot) in shared memory, one barrier, and every thread applies
 //     a_ij -= a_ik a_kj / a_kk  (i, j != k) ;  a_ik = a_ik / a_kk ;  a_kk = -1 / a_kk
-// to its tile: 25 FMAs against 10 shared-memory loads, no index arithmetic in the inner loop.  Sweep<SH>::PAR segments are swept
+// to its tile: 25 FMAs against 10 shared-memory loads, no index arithmetic in the inner loop.
+// Round 2: whole 5 x 5 BLOCKS of pivots are swept at a time (sweep_block_*): with K the diagonal tile of block P,
+//     A_PP <- -K^-1 ;  A_iP <- A_iP K^-1 ;  A_ij <- A_ij - (A_iP K^-1) A_jP^T        (i, j outside P)
+// which is the same map as the five single sweeps but costs three barriers instead of five and moves the five dependent
+// divisions onto one thread (the holder of the diagonal tile inverts it in registers); the pivots behind the last full block
+// (m mod 5 of them) go one by one.  MEASURED SLOWER on B200 (interior sweeps 768 k cycles per OCP against 451 k for the
+// pivot-by-pivot sweep, profiles/r2p_phase_cycles.txt): the rank-5 update triples the shared-memory traffic per tile and the
+// in-register inversion is a 900-cycle serial chain every block.  Kept behind MPCB_SWEEP_BLOCKED (default 0) as a record.  Sweep<SH>::PAR segments are swept
 // at a time (three for the base shape, 153 threads each); the separator Schur complement C (kind == NS) goes through the same
 // code afterwards.
 // Result: W = -S_II^-1, F = S_II^-1 S_IB, S_BB - S_BI S_II^-1 S_IB  (resp. -C^-1), written back in place.
@@ -162,6 +169,11 @@ template <class SH>
 MPCB_DEV int sweep_m(int kind) { return kind < SH::NS ? SH::m(kind) : SH::NB; }            // number of pivots
 template <class SH>
 MPCB_DEV int sweep_M(int kind) { return kind < SH::NS ? SH::m(kind) + SH::nb(kind) : SH::NB; }
+template <class SH>
+#ifndef MPCB_SWEEP_BLOCKED
+#define MPCB_SWEEP_BLOCKED 0
+#endif
+MPCB_DEV int sweep_nblocks(int kind) { return MPCB_SWEEP_BLOCKED ? sweep_m<SH>(kind) / TILE : 0; }   // full 5-pivot blocks (blocked sweep); the rest goes one by one
 template <class SH>
 MPCB_DEV double* sweep_ptr(const Ctx<SH>& c, int kind, int i, int j) {     // entry (i, j), i >= j, of matrix `kind`
     if (kind < SH::NS) return aug_ptr(c, kind, SH::m(kind), SH::nb(kind), i, j);
@@ -200,7 +212,7 @@ MPCB_DEV void sweep_publish(const Ctx<SH>& c, const TS<SH>& ts, int first, int k
     }
 }
 template <class SH>
-MPCB_DEV void sweep_load(const Ctx<SH>& c, TS<SH>& ts, int tid, int first, int count, int slot) {
+MPCB_DEV void sweep_load_tiles(const Ctx<SH>& c, TS<SH>& ts, int tid, int first, int count, int slot) {
     sweep_assign(ts, tid, first, count, slot);
     const int kind = ts.tseg;
     if (kind < 0) return;
@@ -213,13 +225,12 @@ MPCB_DEV void sweep_load(const Ctx<SH>& c, TS<SH>& ts, int tid, int first, int c
             const int hi = i > j ? i : j, lo = i > j ? j : i;
             ts.tile[TILE * x + y] = (hi < M) ? *sweep_ptr(c, kind, hi, lo) : 0.0;
         }
-    sweep_publish<SH, 0>(c, ts, first, 0, 0);
 }
 // pivot kp = 5 P + R: update the tile from buffer (kp & 1), then publish column kp + 1 into the other buffer
 template <class SH, int R>
 MPCB_DEV void sweep_step(const Ctx<SH>& c, TS<SH>& ts, int first, int P) {
     const int kind = ts.tseg, kp = TILE * P + R;
-    if (kind < 0 || kp >= sweep_m<SH>(kind)) return;
+    if (kind < 0 || kp >= sweep_m<SH>(kind) || P < sweep_nblocks<SH>(kind)) return;      // the full blocks went through sweep_block_*
     const double* col = sweep_col(c, kind, first, kp & 1);
     const double dinv = col[Sweep<SH>::COLS - 1];
     double ci[TILE], cj[TILE];
@@ -253,18 +264,149 @@ MPCB_DEV void sweep_store(const Ctx<SH>& c, const TS<SH>& ts) {
             if (i < M && j <= i) *sweep_ptr(c, kind, i, j) = ts.tile[TILE * x + y];
         }
 }
+// ---- blocked sweep ------------------------------------------------------------------------------------------------------------
+// scratch of matrix `kind`: raw panel [M5][5] | scaled panel [M5][5] | K^-1 [25]   (M5 = M rounded up to the tile size)
+template <class SH>
+MPCB_DEV int sweep_M5(int kind) { return (sweep_M<SH>(kind) + TILE - 1) / TILE * TILE; }
+template <class SH>
+MPCB_DEV double* sweep_scratch(const Ctx<SH>& c, int kind, int first) {
+    if (Layout<SH>::GMAT) return c.colbuf + 2 * Sweep<SH>::PAR * Sweep<SH>::COLS + (kind - first) * Sweep<SH>::PANEL;
+    return kind < SH::NS ? c.F + SH::foff(kind) : c.C;       // free while the sweep runs: the content sits in the register tiles
+}
+// (panels are stored k-major: entry (i, k) of a panel at [k * M5 + i], so that the five entries a tile row / column needs are
+// contiguous; the loops below touch one k at a time to keep the register footprint at tile + 10 values)
+// phase 1 of block P: the panel tiles publish their raw content, the diagonal tile is inverted in registers
+template <class SH>
+MPCB_DEV void sweep_block_a(const Ctx<SH>& c, TS<SH>& ts, int first, int P) {
+    const int kind = ts.tseg;
+    if (kind < 0 || P >= sweep_nblocks<SH>(kind)) return;
+    double* pan = sweep_scratch(c, kind, first);
+    const int M5 = sweep_M5<SH>(kind);
+    if (ts.tJ == P && ts.tI > P) {                         // A_IP: entry (5 tI + x, y)
+        MPCB_UNROLL
+        for (int y = 0; y < TILE; y++)
+            MPCB_UNROLL
+            for (int x = 0; x < TILE; x++) pan[y * M5 + TILE * ts.tI + x] = ts.tile[TILE * x + y];
+    } else if (ts.tI == P && ts.tJ < P) {                  // A_PJ = A_JP^T: entry (5 tJ + y, x)
+        MPCB_UNROLL
+        for (int x = 0; x < TILE; x++)
+            MPCB_UNROLL
+            for (int y = 0; y < TILE; y++) pan[x * M5 + TILE * ts.tJ + y] = ts.tile[TILE * x + y];
+    } else if (ts.tI == P && ts.tJ == P) {                 // K -> -K^-1 by five in-register sweeps; K^-1 goes to the scratch
+        MPCB_UNROLL
+        for (int k = 0; k < TILE; k++) {
+            const double d = 1.0 / ts.tile[TILE * k + k];
+            double ci[TILE];
+            MPCB_UNROLL
+            for (int x = 0; x < TILE; x++) ci[x] = ts.tile[TILE * x + k] * d;
+            MPCB_UNROLL
+            for (int x = 0; x < TILE; x++)
+                MPCB_UNROLL
+                for (int y = 0; y < TILE; y++)
+                    if (x != k && y != k) ts.tile[TILE * x + y] -= ci[x] * ts.tile[TILE * k + y];
+            MPCB_UNROLL
+            for (int x = 0; x < TILE; x++)
+                if (x != k) { ts.tile[TILE * x + k] = ci[x]; ts.tile[TILE * k + x] = ci[x]; }
+            ts.tile[TILE * k + k] = -d;
+        }
+        double* kinv = pan + 2 * TILE * M5;
+        MPCB_UNROLL
+        for (int e = 0; e < TILE * TILE; e++) kinv[e] = -ts.tile[e];
+    }
+}
+// phase 2: the panel tiles are scaled by K^-1 (their final value) and published
+template <class SH>
+MPCB_DEV void sweep_block_b(const Ctx<SH>& c, TS<SH>& ts, int first, int P) {
+    const int kind = ts.tseg;
+    if (kind < 0 || P >= sweep_nblocks<SH>(kind)) return;
+    const bool colp = ts.tJ == P && ts.tI > P, rowp = ts.tI == P && ts.tJ < P;
+    if (!colp && !rowp) return;
+    double* pan = sweep_scratch(c, kind, first);
+    const int M5 = sweep_M5<SH>(kind);
+    double* span = pan + TILE * M5;
+    const double* kinv = pan + 2 * TILE * M5;
+    if (colp) {                                            // row x of A_IP K^-1 only needs row x of A_IP
+        MPCB_UNROLL
+        for (int x = 0; x < TILE; x++) {
+            double r[TILE];
+            MPCB_UNROLL
+            for (int y = 0; y < TILE; y++) {
+                double a = 0;
+                MPCB_UNROLL
+                for (int k = 0; k < TILE; k++) a += ts.tile[TILE * x + k] * kinv[TILE * k + y];
+                r[y] = a;
+            }
+            MPCB_UNROLL
+            for (int y = 0; y < TILE; y++) { ts.tile[TILE * x + y] = r[y]; span[y * M5 + TILE * ts.tI + x] = r[y]; }
+        }
+    } else {                                               // column y of K^-1 A_PJ only needs column y of A_PJ
+        MPCB_UNROLL
+        for (int y = 0; y < TILE; y++) {
+            double r[TILE];
+            MPCB_UNROLL
+            for (int x = 0; x < TILE; x++) {
+                double a = 0;
+                MPCB_UNROLL
+                for (int k = 0; k < TILE; k++) a += kinv[TILE * x + k] * ts.tile[TILE * k + y];
+                r[x] = a;
+            }
+            MPCB_UNROLL
+            for (int x = 0; x < TILE; x++) { ts.tile[TILE * x + y] = r[x]; span[x * M5 + TILE * ts.tJ + y] = r[x]; }
+        }
+    }
+}
+// phase 3: every tile outside block row / column P takes the rank-5 update, one k at a time
+template <class SH>
+MPCB_DEV void sweep_block_c(const Ctx<SH>& c, TS<SH>& ts, int first, int P) {
+    const int kind = ts.tseg;
+    if (kind < 0 || P >= sweep_nblocks<SH>(kind) || ts.tI == P || ts.tJ == P) return;
+    const double* pan = sweep_scratch(c, kind, first);
+    const int M5 = sweep_M5<SH>(kind);
+    const double* si = pan + TILE * M5 + TILE * ts.tI;     // scaled entries of block tI
+    const double* pj = pan + TILE * ts.tJ;                 // raw entries of block tJ
+    MPCB_UNROLL
+    for (int k = 0; k < TILE; k++) {
+        double a[TILE], b[TILE];
+        MPCB_UNROLL
+        for (int x = 0; x < TILE; x++) { a[x] = si[k * M5 + x]; b[x] = pj[k * M5 + x]; }
+        MPCB_UNROLL
+        for (int x = 0; x < TILE; x++)
+            MPCB_UNROLL
+            for (int y = 0; y < TILE; y++) ts.tile[TILE * x + y] -= a[x] * b[y];
+    }
+}
+// publish the first single pivot column behind the full blocks (the start of the per-pivot tail)
+template <class SH>
+MPCB_DEV void sweep_publish_tail(const Ctx<SH>& c, const TS<SH>& ts, int first) {
+    const int kind = ts.tseg;
+    if (kind < 0) return;
+    const int kn = TILE * sweep_nblocks<SH>(kind);
+    sweep_publish<SH, 0>(c, ts, first, kn, kn & 1);
+}
 // sweep matrices first .. first+count-1 (count <= Sweep::PAR, `slot` threads each) over all their pivots
 template <class SH>
 MPCB_DEV void sweep_round(MPCB_DRIVER_PARAMS(SH), int first, int count, int slot) {
-    int mmax = 0;
-    for (int k = first; k < first + count; k++) mmax = sweep_m<SH>(k) > mmax ? sweep_m<SH>(k) : mmax;
-    MPCB_PHASE(sweep_load(c, ts, tid, first, count, slot));
-    for (int P = 0; TILE * P < mmax; P++) {
-        MPCB_PHASE(sweep_step<SH, 0>(c, ts, first, P));
-        MPCB_PHASE(sweep_step<SH, 1>(c, ts, first, P));
-        MPCB_PHASE(sweep_step<SH, 2>(c, ts, first, P));
-        MPCB_PHASE(sweep_step<SH, 3>(c, ts, first, P));
-        MPCB_PHASE(sweep_step<SH, 4>(c, ts, first, P));
+    int nbmax = 0, tail_lo = 1 << 30, tail_hi = 0;
+    for (int k = first; k < first + count; k++) {
+        const int nbk = sweep_nblocks<SH>(k), mk = sweep_m<SH>(k);
+        nbmax = nbk > nbmax ? nbk : nbmax;
+        if (mk > TILE * nbk) { const int hi = (mk + TILE - 1) / TILE; tail_lo = nbk < tail_lo ? nbk : tail_lo; tail_hi = hi > tail_hi ? hi : tail_hi; }
+    }
+    MPCB_PHASE(sweep_load_tiles(c, ts, tid, first, count, slot));
+    for (int P = 0; P < nbmax; P++) {
+        MPCB_PHASE(sweep_block_a(c, ts, first, P));
+        MPCB_PHASE(sweep_block_b(c, ts, first, P));
+        MPCB_PHASE(sweep_block_c(c, ts, first, P));
+    }
+    if (tail_hi > 0) {
+        MPCB_PHASE(sweep_publish_tail(c, ts, first));
+        for (int P = tail_lo; P < tail_hi; P++) {
+            MPCB_PHASE(sweep_step<SH, 0>(c, ts, first, P));
+            MPCB_PHASE(sweep_step<SH, 1>(c, ts, first, P));
+            MPCB_PHASE(sweep_step<SH, 2>(c, ts, first, P));
+            MPCB_PHASE(sweep_step<SH, 3>(c, ts, first, P));
+            MPCB_PHASE(sweep_step<SH, 4>(c, ts, first, P));
+        }
     }
     MPCB_PHASE(sweep_store(c, ts));
 }

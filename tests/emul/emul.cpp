@@ -25,7 +25,7 @@ struct Emu {
     double limtab[40];
     int flags[2];
     Emu(const mpcb_settings* st, const mpcb_limits* lim)
-        : smem(Layout<SH>::TOTAL, 0.0), gmat(Layout<SH>::MATDOUBLES, 0.0), z(SH::VP, 0.0), lam(SH::NDUAL + 8, 0.0), qb(QBL<SH>::QPBLOCK, 0.0), jg(SH::NN * 176, 0.0),
+        : smem(Layout<SH>::TOTAL, 0.0), gmat(Layout<SH>::CTA_BLOCK, 0.0), z(SH::VP, 0.0), lam(SH::NDUAL + 8, 0.0), qb(QBL<SH>::QPBLOCK, 0.0), jg(SH::NN * 176, 0.0),
           gj(SH::NINEQ, 0.0), gval(16 * SH::NINEQ, 0.0), tsv(SH::NT) {
         mpcb_fill_cheb(SH::PO, SH::NS, &cheb);
         fill_limtab(lim, limtab);

@@ -63,3 +63,57 @@ def test_mpc_benchmark_rows(tmp_path):
     _, acc = sv.sample(sx, su, sT, target=xT, npts=200, want_traj=False)
     assert np.abs(a[:, 126:140] - acc["final_err"]).max() < 1e-5
     sv.close()
+
+
+# ---- the reference's OWN mains, compiled unchanged against shim/ (SURVEY hard part H5; `make examples-unchanged`) ----------------------
+REF = "/root/reference"
+REF_OFF = os.path.join(ROOT, "build", "ref_offline_trajectory")
+REF_BEN = os.path.join(ROOT, "build", "ref_mpc_benchmark")
+
+
+def test_reference_mains_compile_unchanged():
+    """/root/reference/examples/{offline_trajectory,benchmark}.cpp compile without edits against shim/motionPlanner.hpp (a minimal
+    Eigen / pinocchio surface + an Eigen-typed adapter over include/motion_planner.hpp).  Needs the reference tree (this container)."""
+    if not os.path.isdir(os.path.join(REF, "examples")):
+        pytest.skip("reference tree not mounted")
+    subprocess.check_call(["make", "-s", "-C", ROOT, "examples-unchanged"])
+    assert os.path.exists(REF_OFF) and os.path.exists(REF_BEN)
+    import torch
+    if not torch.cuda.is_available():
+        r = subprocess.run([REF_OFF], capture_output=True, text=True, cwd=ROOT)
+        assert r.returncode != 0 and "no CUDA device" in (r.stderr + r.stdout)
+
+
+@pytest.mark.gpu
+def test_reference_offline_main_matches_ported_main(tmp_path):
+    """The unchanged reference main writes analysis/optimal_solution.txt (403 x 29); with the same seed the ported main writes the same
+    numbers to the 6 digits both print."""
+    if not os.path.exists(REF_OFF):
+        pytest.skip("build/ref_offline_trajectory not built (make examples-unchanged needs the reference tree)")
+    off, _ = _build()
+    (tmp_path / "analysis").mkdir()
+    r = subprocess.run([REF_OFF], capture_output=True, text=True, timeout=300, cwd=tmp_path)
+    if r.returncode != 0 and "outside bounds" in (r.stderr + r.stdout):
+        pytest.skip("the seed-0 states fall outside the margins (the reference main throws there)")
+    assert r.returncode == 0, r.stderr
+    a = np.loadtxt(tmp_path / "analysis" / "optimal_solution.txt")
+    assert a.shape == (403, 29)
+    out = tmp_path / "ported.txt"
+    r = subprocess.run([off, str(out), "0"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    b = np.loadtxt(out)
+    assert np.abs(a - b).max() <= 1e-5 * max(1.0, np.abs(b).max())
+
+
+@pytest.mark.gpu
+def test_reference_benchmark_main_rows(tmp_path):
+    """The unchanged reference mpc_benchmark main: 1000 sequential solves through one planner, one 162-column row each."""
+    if not os.path.exists(REF_BEN):
+        pytest.skip("build/ref_mpc_benchmark not built (make examples-unchanged needs the reference tree)")
+    (tmp_path / "analysis").mkdir()
+    r = subprocess.run([REF_BEN], capture_output=True, text=True, timeout=600, cwd=tmp_path)
+    assert r.returncode == 0, r.stderr[-2000:]
+    a = np.loadtxt(tmp_path / "analysis" / "benchmark_data.txt")
+    assert a.shape == (1000, 162)
+    assert set(np.unique(a[:, 140:148])) <= {0.0, 1.0}
+    assert np.all(a[:, 56:84] <= a[:, 84:112] + 1e-12) and np.all(a[:, 0:28] <= a[:, 28:56] + 1e-12)

@@ -267,3 +267,31 @@ def test_bad_arguments_are_rejected(solver):
     assert L.mpcb_solve_batch(solver.h, C.c_int(-1), None, None, None, None, None, None, None, None, None, None, None, 0, None) == -2
     assert L.mpcb_solve_batch(solver.h, C.c_int(1), None, None, None, None, None, None, None, None, None, None, None, 0, None) == -2
     assert L.mpcb_solve_batch(solver.h, C.c_int(0), None, None, None, None, None, None, None, None, None, None, None, 0, None) == 0
+
+
+def test_profile_sampling_and_accounting_on_device(oracle, solver):
+    """The warm-start ("Ruckig") half of the benchmark on the device (mpcb_sample_profile_batch, examples/benchmark.cpp:72-114): samples
+    equal the host profile generator's, torques the oracle's RNEA, flags / extrema / final error the oracle's accounting."""
+    s, lim, x0, xT, gx, gu, gT = _problems(0, 6, 40, BENCH_MARGINS)
+    x0 = x0.copy(); xT = xT.copy()
+    xT[7, 7] = 1.01 * BENCH_MARGINS[1] * lim.vmax[0]          # one rejected input: the cubic-Hermite fallback
+    gx, gu, gT = M.guess_batch(s, lim, x0, xT)
+    solver.set_limits(lim)
+    traj, acc, T = solver.sample_profile(x0, xT, npts=200)
+    assert np.abs(T - gT).max() <= 1e-12 * np.abs(gT).max()
+    lo = oracle.default_limits(BENCH_MARGINS)
+    for i in (0, 3, 7, 21, 39):
+        rc, tr = M.otg_calculate(lim, x0[i], xT[i])
+        if i != 7:
+            assert rc >= 0
+            for p in (0, 1, 57, 133, 200):
+                q, v, a = M.otg_at_time(tr, tr.T / 200 * p)
+                assert np.abs(traj[i, p, 1:8] - q).max() < 1e-10 and np.abs(traj[i, p, 8:15] - v).max() < 1e-10 and np.abs(traj[i, p, 15:22] - a).max() < 1e-7
+        else:
+            assert rc < 0
+        for p in (0, 99, 200):
+            assert np.abs(traj[i, p, 22:29] - oracle.rnea(traj[i, p, 1:8], traj[i, p, 8:15], traj[i, p, 15:22])).max() < 1e-9
+        oa = oracle.account(lo, traj[i], xT[i])
+        assert list(acc[i]["flags"]) == list(oa.flags)
+        assert np.abs(acc[i]["mins"] - np.array(oa.mins)).max() < 1e-9 and np.abs(acc[i]["maxs"] - np.array(oa.maxs)).max() < 1e-9
+        assert np.abs(acc[i]["final_err"] - np.array(oa.final_err)).max() < 1e-9

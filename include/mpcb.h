@@ -125,6 +125,25 @@ int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, 
                      double* sol_u, double* sol_T, double* sol_lam, mpcb_stats* stats, int mem, void* stream);
 
 /*
+ * mpcb_solve_batch for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.
+ * Same kernels, arguments and results as mpcb_solve_batch with MPCB_MEM_DEVICE (every pointer is a device pointer on the handle's
+ * device; the call only enqueues work on `stream`), but the per-OCP solver workspace and the work counters live in file-scope
+ * static __device__ arrays of libmpcb instead of buffers the handle allocates, and the call makes no cudaMalloc / cudaFree / event
+ * creation.  Limit: n <= MPCB_NOALLOC_MAX_OCPS for every collocation shape; the static workspace is sized for that many problems
+ * of the base shape (3,6), which has the largest per-OCP workspace (8 x 539 KB = 4.3 MB of device memory, held by every GPU that
+ * loads the library until the process exits).  n beyond the limit returns
+ * MPCB_ERR_BAD_ARG with the limit in mpcb_last_error; nothing is enqueued.  The scratch is shared by ALL handles and calls of
+ * the process on that device and keeps the last call's contents (the call resets what must start at zero: the work counters):
+ * calls that overlap on the GPU (different streams or handles, no ordering between them) race -- order them on one stream or with
+ * events.  The per-kernel timers (mpcb_last_solve_ms, mpcb_last_kernel_ms) are not updated by this entry point.
+ */
+#define MPCB_NOALLOC_MAX_OCPS 8
+int mpcb_solve_batch_noalloc(mpcb_handle* h, int n, const double* x0, const double* xT, const double* guess_x,
+                             const double* guess_u, const double* guess_T, const double* guess_lam, double* sol_x,
+                             double* sol_u, double* sol_T, double* sol_lam, mpcb_stats* stats, void* stream);
+
+/*
  * Read-out + accounting (get_MPC_trajectory<npts>, motionPlanner.hpp:99-116; benchmark.cpp:118-194):
  *   traj   n x (npts+1) x 29  rows [t, q(7), v(7), a(7), tau(7)]  (may be NULL)
  *   acc    n                  (may be NULL);   target n x 14 (needed when acc != NULL)

@@ -55,6 +55,7 @@ assert STATS_DTYPE.itemsize == C.sizeof(Stats), (STATS_DTYPE.itemsize, C.sizeof(
 assert ACCOUNT_DTYPE.itemsize == C.sizeof(Account)
 
 MEM_HOST, MEM_DEVICE = 0, 1
+NOALLOC_MAX_OCPS = 8      # MPCB_NOALLOC_MAX_OCPS of include/mpcb.h (base shape)
 
 
 def lib_path():
@@ -217,6 +218,14 @@ class Solver:
                                      _p(sT), _p(slam) if slam else None, _p(stats) if stats else None, C.c_int(MEM_DEVICE),
                                      C.c_void_p(stream) if stream else None)
         self._check(rc, "mpcb_solve_batch")
+
+    def solve_device_noalloc(self, n, x0, xT, gx, gu, gT, glam, sx, su, sT, slam, stats, stream=0):
+        """mpcb_solve_batch_noalloc: solve_device over the library's static device scratch (n <= NOALLOC_MAX_OCPS of the base shape);
+        makes no allocation.  Calls that overlap on the GPU share (and race on) that scratch."""
+        rc = self.L.mpcb_solve_batch_noalloc(self.h, C.c_int(n), _p(x0), _p(xT), _p(gx), _p(gu), _p(gT), _p(glam) if glam else None, _p(sx),
+                                             _p(su), _p(sT), _p(slam) if slam else None, _p(stats) if stats else None,
+                                             C.c_void_p(stream) if stream else None)
+        self._check(rc, "mpcb_solve_batch_noalloc")
 
     def guess(self, x0, xT):
         """warm_start_RK for a batch on the device (mpcb_guess_batch_gpu, host arrays in and out)."""

@@ -294,6 +294,56 @@ int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, 
     return MPCB_OK;
 }
 
+// No-allocation variant of mpcb_solve_batch (device pointers only; no counterpart in the reference): the same launch sequence over
+// the static __device__ scratch of mpcb_kernels.cu (noalloc_scratch), without the handle's lazily grown buffers and event list.
+int mpcb_solve_batch_noalloc(mpcb_handle* h, int n, const double* x0, const double* xT, const double* guess_x, const double* guess_u,
+                             const double* guess_T, const double* guess_lam, double* sol_x, double* sol_u, double* sol_T, double* sol_lam,
+                             mpcb_stats* stats, void* stream_) {
+    if (!h) return MPCB_ERR_BAD_ARG;
+    if (n < 0 || (n > 0 && (!x0 || !xT || !guess_x || !guess_u || !guess_T || !sol_x || !sol_u || !sol_T))) { h->err = "null or negative argument"; return MPCB_ERR_BAD_ARG; }
+    if (n == 0) return MPCB_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    CK(cudaSetDevice(h->device));
+    double* ws = nullptr; int* counters = nullptr; size_t ws_doubles = 0; int n_counters = 0;
+    CK(noalloc_scratch(h->device, &ws, &ws_doubles, &counters, &n_counters));      // cudaGetSymbolAddress, first call per device only
+    size_t limit = ws_doubles / h->si.ws_doubles;                 // the base shape has the largest per-OCP workspace
+    if (limit > (size_t)MPCB_NOALLOC_MAX_OCPS) limit = MPCB_NOALLOC_MAX_OCPS;
+    if ((size_t)n > limit) {
+        h->err = "mpcb_solve_batch_noalloc: n = " + std::to_string(n) + " exceeds the static scratch, which holds at most " + std::to_string(limit) +
+                 " OCPs (MPCB_NOALLOC_MAX_OCPS); use mpcb_solve_batch or split the batch";
+        return MPCB_ERR_BAD_ARG;
+    }
+    const int n_launch = 2 + 3 * h->st.sqp_max_iter;
+    if (n_launch > n_counters) { h->err = "mpcb_solve_batch_noalloc: sqp_max_iter too large for the static work counters"; return MPCB_ERR_BAD_ARG; }
+    CK(handle_enter(h, stream));
+    BatchPtrs bp;
+    memset(&bp, 0, sizeof bp);
+    bp.x0 = x0; bp.xT = xT; bp.gx = guess_x; bp.gu = guess_u; bp.gT = guess_T; bp.glam = guess_lam;
+    bp.sx = sol_x; bp.su = sol_u; bp.sT = sol_T; bp.slam = sol_lam; bp.stats = stats;
+    const int grid = n < h->grid_max ? n : h->grid_max;
+    CK(cudaMemsetAsync(counters, 0, sizeof(int) * n_launch, stream));      // the only part of the scratch that must start at zero
+    int li = 0;
+    const bool generic = settings_generic_path(&h->st) != 0;
+    CK(launch_sqp_stage(h->kc, bp, n, 0, 0, grid, counters + li++, ws, h->d_gmat, h->d_prof, stream));
+    long long launched = 1;
+    for (int it = 1; it <= h->st.sqp_max_iter; it++) {
+        CK(launch_node_jac(h->kc, n, ws, stream));
+        if (generic) {
+            CK(launch_sqp_stage(h->kc, bp, n, 3, it, grid, counters + li++, ws, h->d_gmat, h->d_prof, stream));
+            launched += 4;
+        } else {
+            CK(launch_sqp_stage(h->kc, bp, n, 1, it, grid, counters + li++, ws, h->d_gmat, h->d_prof, stream));
+            CK(launch_admm(h->kc, n, grid, counters + li++, ws, h->d_prof, stream));
+            launched += 5;
+        }
+        CK(launch_node_val(h->kc, n, ws, stream));
+        CK(launch_sqp_stage(h->kc, bp, n, 2, it, grid, counters + li++, ws, h->d_gmat, h->d_prof, stream));
+    }
+    h->launches += launched;
+    CK(handle_leave(h, stream));
+    return MPCB_OK;
+}
+
 int mpcb_sample_batch(mpcb_handle* h, int n, const double* sol_x, const double* sol_u, const double* sol_T, const double* target,
                       int npts, double* traj, mpcb_account* acc, int mem, void* stream_) {
     if (!h) return MPCB_ERR_BAD_ARG;

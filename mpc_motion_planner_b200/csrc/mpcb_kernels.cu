@@ -9,6 +9,7 @@
 //   fp64_peak_kernel: FP64 FMA throughput micro-benchmark (roofline denominator)
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <mutex>
 
 #include "mpcb_kernels.h"
 #include "mpcb_gen.h"
@@ -528,6 +529,41 @@ cudaError_t launch_node_debug(int n, const double* qva, double* g_val, double* g
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream) {
     fp64_peak_kernel<<<blocks, threads, 0, stream>>>(out, iters);
     return cudaGetLastError();
+}
+
+// ---- scratch of the no-allocation solve (mpcb_solve_batch_noalloc; no counterpart in the reference, added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops) -----------------------------------------
+// The per-OCP workspace (iterate, multipliers, node Jacobians, factorised QP block) and the work counters of the persistent kernels
+// live in file-scope device arrays instead of the handle's cudaMalloc'ed buffers: MPCB_NOALLOC_MAX_OCPS problems of the base shape
+// (4.3 MB; every GPU that loads libmpcb holds it until exit).  In host code the array names are host-side stand-ins, not device
+// addresses: the device addresses are looked up once per device with cudaGetSymbolAddress (that device current) and handed to the
+// same kernels the allocating path launches.  All handles and all calls share the arrays.
+static constexpr size_t NOALLOC_WS_DOUBLES = (size_t)MPCB_NOALLOC_MAX_OCPS * WS<SH36>::STRIDE;
+static constexpr int NOALLOC_COUNTERS = 64;
+static __device__ __align__(256) double g_noalloc_workspace[NOALLOC_WS_DOUBLES];
+static __device__ __align__(256) int g_noalloc_counters[NOALLOC_COUNTERS];
+
+cudaError_t noalloc_scratch(int device, double** workspace, size_t* workspace_doubles, int** counters, int* n_counters) {
+    static std::mutex mu;
+    static double* ws_of[64];
+    static int* ctr_of[64];
+    static bool have[64];
+    if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!have[device]) {
+        int cur = -1;
+        cudaError_t e = cudaGetDevice(&cur);
+        if (e != cudaSuccess) return e;
+        if (cur != device) return cudaErrorInvalidDevice;       // the caller makes the handle's device current first
+        void *pw = nullptr, *pc = nullptr;
+        if ((e = cudaGetSymbolAddress(&pw, g_noalloc_workspace)) != cudaSuccess) return e;
+        if ((e = cudaGetSymbolAddress(&pc, g_noalloc_counters)) != cudaSuccess) return e;
+        ws_of[device] = static_cast<double*>(pw); ctr_of[device] = static_cast<int*>(pc);
+        have[device] = true;
+    }
+    *workspace = ws_of[device]; *workspace_doubles = NOALLOC_WS_DOUBLES;
+    *counters = ctr_of[device]; *n_counters = NOALLOC_COUNTERS;
+    return cudaSuccess;
 }
 
 }  // namespace mpcb

@@ -60,5 +60,8 @@ cudaError_t launch_gen_problems(const mpcb_limits& lim, int kind, unsigned long 
 // debug: node_constraints_value / node_constraints_jac of n states (q, v, a) on the device
 cudaError_t launch_node_debug(int n, const double* qva, double* g_val, double* g_jac, double* Jg, cudaStream_t stream);
 cudaError_t launch_fp64_peak(double* out, int blocks, int threads, int iters, cudaStream_t stream);
+// scratch of mpcb_solve_batch_noalloc: device addresses of the file-scope static __device__ arrays of mpcb_kernels.cu on `device`
+// (which must be current), looked up once per device
+cudaError_t noalloc_scratch(int device, double** workspace, size_t* workspace_doubles, int** counters, int* n_counters);
 
 }  // namespace mpcb

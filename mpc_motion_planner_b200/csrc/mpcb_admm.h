@@ -260,6 +260,26 @@ constexpr int ANT = MPCB_ADMM_WIDE ? NT : NT / 2;
     }
 #endif
 
+// Prefetch of thread-private constant operands (tensor memory) across the barrier that ends the previous phase: the device issues
+// the load before the barrier and hands the buffer to the consumer; the lock-step host emulation (one thread at a time, a phase
+// at a time) declares the buffer inside the consuming phase and loads it there (same values: the strips are constant during a QP).
+// which phases prefetch (device): bit 0 = first W overflow chunk (phase B).  The same for C^-1 (phase C), the F row (phase D) and the
+// row / box constants (phase E) was measured and is NOT done: holding their 16..36 destination registers across the barrier pushes the
+// 128-register kernel into spills (30.8 k -> 27.9 k OCP/s with D or E, 21.9 k with C)
+#ifndef MPCB_PRE_MASK
+#define MPCB_PRE_MASK 1
+#endif
+constexpr bool PRE_B = MPCB_PRE_MASK & 1;
+#ifdef MPCB_EMUL
+#define MPCB_PRE_ON false
+#define MPCB_PRE_DECL(type, name) type name;
+#define MPCB_PRE(...)
+#else
+#define MPCB_PRE_ON true
+#define MPCB_PRE_DECL(type, name) type name;
+#define MPCB_PRE(...) __VA_ARGS__
+#endif
+
 struct d2 { double a, b; };
 MPCB_DEV d2 ld2(const double* p) {          // 16-byte load (p is 16-byte aligned by construction of the layouts)
 #ifdef MPCB_EMUL
@@ -503,40 +523,47 @@ MPCB_DEV void w_slots(const double* x, const COEF& coef, double* acc) {
     MPCB_UNROLL
     for (int e = E0; e < (E1 < R * STEPS ? E1 : R * STEPS); e++) acc[e % R] += coef(e) * x[e / R];
 }
-// one thread's R x STEPS block of W times the vector: registers first, then the TMEM overflow chunk by chunk (16 slots each)
-template <class SH, int KIND, int R, int STEPS>
-MPCB_DEV void w_block(ACtx<SH>& c, ATS<SH>& ts, int tid, const double* b, double* acc) {
+// one thread's R x STEPS block of W times the vector.  The first TMEM overflow chunk (16 slots) arrives in `pre`: on the device it
+// is loaded BEFORE the barrier that ends phase A (w_prefetch: thread-private constant data, so the barrier wait hides the tensor-memory
+// latency); the host emulation loads it here.  Order: chunk 0 | second chunk requested | register coefficients (cover its latency) |
+// second chunk.
+template <class SH, int KIND, int R, int STEPS, bool PRE>
+MPCB_DEV void w_block(ACtx<SH>& c, ATS<SH>& ts, int tid, const double* b, double* acc, TmBuf<16>& ch0) {
     typedef AL<SH> L;
     constexpr int W = L::WREG, NCH = L::wchunks(KIND);
-    TmBuf<16> ch0;
-    if constexpr (NCH > 0) tm_ld(ts.tma(), L::tm_wov(tid), ch0);
-    double x[STEPS];                                   // the vector entries are read while the tensor-memory load is in flight
+    static_assert(NCH >= 1 && NCH <= 2, "one or two overflow chunks");
+    if constexpr (!PRE) tm_ld(ts.tma(), L::tm_wov(tid), ch0);
+    double x[STEPS];
     MPCB_UNROLL
     for (int t = 0; t < STEPS; t++) x[t] = b[8 * t];
-    w_slots<R, STEPS, 0, W>(x, [&](int e) { return ts.wreg[e]; }, acc);
-    if constexpr (NCH > 0) {
-        tm_wait(ch0);
-        w_slots<R, STEPS, W, W + 16>(x, [&](int e) { return ch0.get(e - W); }, acc);
-    }
+    tm_wait(ch0);
+    w_slots<R, STEPS, W, W + 16>(x, [&](int e) { return ch0.get(e - W); }, acc);
     if constexpr (NCH > 1) {
         TmBuf<16> ch1;
-        tm_ld(ts.tma(), L::tm_wov(tid) + 16, ch1);
+        tm_ld_after(ts.tma(), L::tm_wov(tid) + 16, ch1, x);
+        w_slots<R, STEPS, 0, W>(x, [&](int e) { return ts.wreg[e]; }, acc);
         tm_wait(ch1);
         w_slots<R, STEPS, W + 16, W + 32>(x, [&](int e) { return ch1.get(e - W - 16); }, acc);
+    } else {
+        w_slots<R, STEPS, 0, W>(x, [&](int e) { return ts.wreg[e]; }, acc);
     }
-    static_assert(NCH <= 2, "at most two overflow chunks");
 }
+// device: request the first overflow chunk of the thread's W block (every kind has one, at the same strip offset)
 template <class SH>
-MPCB_DEV void b_w(ACtx<SH>& c, ATS<SH>& ts, int tid) {
+MPCB_DEV void w_prefetch(ATS<SH>& ts, int tid, TmBuf<16>& ch0) {
+    tm_ld(ts.tma(), AL<SH>::tm_wov(tid), ch0);
+}
+template <class SH, bool PRE>
+MPCB_DEV void b_w(ACtx<SH>& c, ATS<SH>& ts, int tid, TmBuf<16>& ch0) {
     typedef AL<SH> L;
     const WRole r = wrole<SH>(tid);
     const double* b = c.rhs + L::ibase(r.seg) + r.q;
     double v[8];
     MPCB_UNROLL
     for (int i = 0; i < 8; i++) v[i] = 0;
-    if (r.kind == 0) w_block<SH, 0, 4, 8>(c, ts, tid, b, v);
-    else if (r.kind == 1) w_block<SH, 1, 7, 7>(c, ts, tid, b, v);
-    else w_block<SH, 2, 4, 9>(c, ts, tid, b, v);
+    if (r.kind == 0) w_block<SH, 0, 4, 8, PRE>(c, ts, tid, b, v, ch0);
+    else if (r.kind == 1) w_block<SH, 1, 7, 7, PRE>(c, ts, tid, b, v, ch0);
+    else w_block<SH, 2, 4, 9, PRE>(c, ts, tid, b, v, ch0);
 #ifdef MPCB_EMUL
     for (int i = 0; i < 8; i++) ts.pv[i] = v[i];
 #else
@@ -794,13 +821,15 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
     MPCB_APHASE(a_load(c, ts, tid));
     MPCB_PROF(0)
     const int max_iter = c.st->qp_max_iter, chk = c.st->qp_check_termination;
+    int until_chk = chk > 0 ? chk : -1;          // iterations left until the next residual test (a countdown: no integer division per iteration)
     for (int iter = 1; iter <= max_iter; iter++) {
         MPCB_WSTAMP(15)
         MPCB_APHASE_NS(a_rhs(c, ts, tid));
-        MPCB_APHASE({ a_rhs_p(c, tid); MPCB_WSTAMP(0) });
+        MPCB_PRE_DECL(TmBuf<16>, wch0)
+        MPCB_APHASE({ a_rhs_p(c, tid); MPCB_PRE(if constexpr (PRE_B) w_prefetch(ts, tid, wch0)); MPCB_WSTAMP(0) });
         MPCB_PROF(1)
         // t = W rhs_I, published in the x~ slots of the interior variables (phase D overwrites them with x~_I = t - F x~_B)
-        MPCB_APHASE_NS(b_w(c, ts, tid));
+        MPCB_APHASE_NS((b_w<SH, MPCB_PRE_ON && PRE_B>(c, ts, tid, wch0)));
         MPCB_APHASE({
             MPCB_WREDUCE_EMUL()
             const WRole r = wrole<SH>(tid);
@@ -839,7 +868,8 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
         MPCB_APHASE({ e_update(c, ts, tid); MPCB_WSTAMP(5) });
         MPCB_WSTAMP(6)
         MPCB_PROF(6)
-        if (chk > 0 && iter % chk == 0) {
+        if (--until_chk == 0) {
+            until_chk = chk;
             MPCB_APHASE(chk_a(c, ts, tid));
             MPCB_APHASE(chk_b(c, ts, tid));
             MPCB_APHASE(chk_c(c, ts, tid, iter));

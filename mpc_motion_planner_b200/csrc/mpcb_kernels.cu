@@ -138,6 +138,9 @@ admm_kernel(const __grid_constant__ KernelConst kc, const int n, int* __restrict
         const uint32_t lanes = (uint32_t)(32 * (w0 & 3)) << 16;
         ts0.tmaddr = tmem_base + lanes + 2 * tm_warp_base(w0);
         ts1.tmaddr = tmem_base + lanes + 2 * tm_warp_base(w1);
+        // opaque to the compiler from here on: otherwise it re-derives the strip address from threadIdx in front of every tcgen05.ld
+        // (5 integer instructions per load, 565 warp instructions per iteration, profiles/r2s_admm_kernel_instmix.txt)
+        asm volatile("" : "+r"(ts0.tmaddr), "+r"(ts1.tmaddr));
     }
     for (;;) {
         if (ptid == 0) s_next = atomicAdd(counter, 1);

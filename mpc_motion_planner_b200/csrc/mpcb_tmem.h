@@ -28,6 +28,8 @@ struct TmBuf {
 template <int N>
 inline void tm_ld(const double* strip, int slot, TmBuf<N>& b) { for (int j = 0; j < N; j++) b.d[j] = strip[slot + j]; }
 template <int N>
+inline void tm_ld_after(const double* strip, int slot, TmBuf<16>& b, double (&)[N]) { tm_ld(strip, slot, b); }
+template <int N>
 inline void tm_wait(TmBuf<N>&) {}
 template <int N, int M>
 inline void tm_wait(TmBuf<N>&, TmBuf<M>&) {}
@@ -71,6 +73,18 @@ __device__ __forceinline__ void tm_ld(uint32_t addr, int slot, TmBuf<16>& b) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];\n"
         : MPCB_TM_O8(b, 0), MPCB_TM_O8(b, 8), MPCB_TM_O8(b, 16), MPCB_TM_O8(b, 24)
+        : "r"(addr + 2 * slot));
+}
+// the same load with an ordering handle: `dep` (register values the following arithmetic reads) passes through the statement, so the
+// compiler cannot schedule that arithmetic in front of the load (it otherwise sinks the load behind every independent multiply-add
+// to shorten the live range of the 32 destination registers, and the tensor-memory latency is exposed)
+template <int N>
+__device__ __forceinline__ void tm_ld_after(uint32_t addr, int slot, TmBuf<16>& b, double (&dep)[N]) {
+    static_assert(N >= 7, "at least seven values order the load");
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%39];\n"
+        : MPCB_TM_O8(b, 0), MPCB_TM_O8(b, 8), MPCB_TM_O8(b, 16), MPCB_TM_O8(b, 24), "+d"(dep[0]), "+d"(dep[1]), "+d"(dep[2]), "+d"(dep[3]), "+d"(dep[4]),
+          "+d"(dep[5]), "+d"(dep[6])
         : "r"(addr + 2 * slot));
 }
 // dependency-only pass of a buffer's registers through an (empty) volatile asm: keeps their uses behind the wait

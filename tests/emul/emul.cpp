@@ -130,7 +130,7 @@ int emul_kkt_apply(const mpcb_settings* st, const mpcb_limits* lim, const double
         if (L::decode(i, k, comp)) c.rhs[i] = rhs[ext_index<SH>(k, comp)];
     }
     c.sc[0] = 0;        // no A^T w gather in this test: rhs is given directly
-    MPCB_PHASE_NS(b_w(c, ts, tid));
+    MPCB_PHASE_NS({ TmBuf<16> wch0; b_w<SH, false>(c, ts, tid, wch0); });
     MPCB_PHASE({ MPCB_WREDUCE_EMUL() const WRole r = wrole<SH>(tid); ts.t = ts.acc; if (r.valid && r.half == 0) c.xt[r.out] = ts.t; b_w_p(c, tid); });
     for (int j = 0; j < 32; j++) c.psum[j] = 0;        // no A^T w gather in this test
     MPCB_PHASE_NS(b_sbi(c, ts, tid));

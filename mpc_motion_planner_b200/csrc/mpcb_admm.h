@@ -437,12 +437,26 @@ MPCB_DEV void a_load(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 #endif
 }
 
-// ---- phase A: rhs = sigma x - h + rho_b z_b - y_b + A^T w ;  warp 13 folds the products A[r,p] w_r into 32 partial sums ----
+// 32 strided partial sums of a dot product of two vectors of length 416 by warp `w` (no shuffle butterfly: ~230 cycles of pure latency
+// at the end of an interval); one lane adds them up in a later interval (b_sbi)
+template <class SH>
+MPCB_DEV void p_partial(int tid, int w, const double* a, const double* b, double* out32) {
+    if ((tid >> 5) != w) return;
+    const double* p = a + (tid & 31);
+    const double* q = b + (tid & 31);
+    double a0 = p[0] * q[0], a1 = p[32] * q[32], a2 = p[64] * q[64], a3 = p[96] * q[96];
+    a0 += p[128] * q[128]; a1 += p[160] * q[160]; a2 += p[192] * q[192]; a3 += p[224] * q[224];
+    a0 += p[256] * q[256]; a1 += p[288] * q[288]; a2 += p[320] * q[320]; a3 += p[352] * q[352];
+    a0 += p[384] * q[384];
+    out32[tid & 31] = (a0 + a1) + (a2 + a3);
+}
+// ---- phase A: rhs = sigma x - h + rho_b z_b - y_b + A^T w  (the p entry of A^T w is added in phase C, see b_sbi) ----
 // Straight-line (branch-free) so that the compiler can interleave the loads of the two logical threads a physical thread
 // runs: conditions become zero coefficients (dt[20] holds 0.0) and clamped addresses, the store is predicated.
 template <class SH>
 MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
+    if (tid >= L::PTID + 32) return;                  // warps 14, 15 own no variable (warp-uniform)
     const bool isp = tid == L::PTID;
     const int ii = tid < L::IP ? tid : 0;
     const int s = (ii / L::SEG) > 5 ? 5 : (ii / L::SEG), rem = ii - L::SEG * s;
@@ -474,21 +488,6 @@ MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     const double r = c.st->qp_sigma * ts.x - h + ts.rhoB * ts.zB - ts.yB + g;
     if (valid || isp) c.rhs[isp ? L::IP : tid] = r;
 }
-// (A^T w)_p = sum_r A[r,p] w_r in two steps that stay off the critical path: logical warp 14 (it owns no variable) forms
-// 32 strided partial sums here without the 5-step shuffle butterfly (~230 cycles of pure latency at the end of the
-// interval), one lane adds them up in the next interval (b_w_finish).
-template <class SH>
-MPCB_DEV void a_rhs_p(ACtx<SH>& c, int tid) {
-    if ((tid >> 5) != 14) return;
-    const double* p = c.pcv + (tid & 31);
-    const double* q = c.w + (tid & 31);
-    double a0 = p[0] * q[0], a1 = p[32] * q[32], a2 = p[64] * q[64], a3 = p[96] * q[96];
-    a0 += p[128] * q[128]; a1 += p[160] * q[160]; a2 += p[192] * q[192]; a3 += p[224] * q[224];
-    a0 += p[256] * q[256]; a1 += p[288] * q[288]; a2 += p[320] * q[320]; a3 += p[352] * q[352];
-    a0 += p[384] * q[384];
-    c.psum[tid & 31] = (a0 + a1) + (a2 + a3);
-}
-
 // ---- phase B: t = W rhs_I from the register-resident rows ------------------------------------------------------------
 // transpose-reduce of R partial sums over the 8 lanes of a group: lane q ends with the full sum of local row
 // (R = 8: 4 b2 + 2 b1 + b0 ; R = 4: 2 b2 + b1, on both lanes of a pair) where b2 b1 b0 are the bits of q
@@ -586,22 +585,12 @@ MPCB_DEV void b_sbi(ACtx<SH>& c, ATS<SH>& ts, int tid) {
         a0 += kv[4] * tv[4]; a1 += kv[5] * tv[5]; a2 += kv[6] * tv[6];
     }
     ts.acc = (a0 + a1) + (a2 + a3);
-    // the two dot products of r_B[p] = rhs_p + (A^T w)_p - (F^T rhs_I)_p arrive as 32 partial sums each (phase A: a_rhs_p, phase B:
-    // b_w_p); two threads of warps that idle in this interval add them up, phase C combines them while it loads r_B
+    // the two dot products of r_B[p] = rhs_p + (A^T w)_p - (F^T rhs_I)_p arrive as 32 partial sums each (phase A: p_partial by warp 14,
+    // which owns no variable; phase B: by warp 3, whose W blocks are the shortest); two threads of warps that idle in this interval add
+    // them up, phase C combines them while it loads r_B.  (Both dot products as shuffle butterflies of idle warps in this interval
+    // were measured: 32.5 k -> 31.9 k OCP/s, the butterfly warps become the last ones of the interval.)
     if (tid == 10 * 32) c.sc[0] = tree32(c.psum);
     if (tid == 11 * 32) c.sc[1] = tree32(c.psum + 32);
-}
-// (F^T rhs_I)_p = sum_i F[i,p] rhs_i as 32 strided partial sums (phase B, the warp with the fewest W rows)
-template <class SH>
-MPCB_DEV void b_w_p(ACtx<SH>& c, int tid) {
-    if ((tid >> 5) != 15) return;
-    const double* p = c.fpc + (tid & 31);
-    const double* q = c.rhs + (tid & 31);
-    double a0 = p[0] * q[0], a1 = p[32] * q[32], a2 = p[64] * q[64], a3 = p[96] * q[96];
-    a0 += p[128] * q[128]; a1 += p[160] * q[160]; a2 += p[192] * q[192]; a3 += p[224] * q[224];
-    a0 += p[256] * q[256]; a1 += p[288] * q[288]; a2 += p[320] * q[320]; a3 += p[352] * q[352];
-    a0 += p[384] * q[384];
-    c.psum[32 + (tid & 31)] = (a0 + a1) + (a2 + a3);
 }
 // ---- phase C: x~_B = C^-1 r_B, 4 lanes per row ------------------------------------------------------------------------
 template <class SH>
@@ -687,6 +676,12 @@ MPCB_DEV void d_interior(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 }
 // ---- phase E: rows and variables update --------------------------------------------------------------------
 // y/rho is evaluated as y * (1/rho) with the reciprocal taken once per QP (an FP64 division costs ~130 cycles of latency).
+#ifndef MPCB_PW
+#define MPCB_PW 3          // the warp that forms the partial sums of (F^T rhs_I)_p in phase B
+#endif
+#ifndef MPCB_EFLAT
+#define MPCB_EFLAT 1
+#endif
 template <class SH>
 MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
@@ -697,6 +692,22 @@ MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     if (tid < SH::NA) ax = row_times(c, tid, c.xt);
     int i, kk, comp;
     const bool var = vrole<SH>(tid, i, kk, comp);
+#if MPCB_EFLAT
+    // straight-line: the row and the variable update are two independent dependent chains of ~10 FP64 operations each; as two guarded
+    // blocks they run one after the other, as one block they interleave.  Threads without a row / a variable update state nobody reads
+    // (every reader is guarded by the same role test), with finite operands (their state and strip constants are zero).
+    xt = c.xt[var ? i : 0];
+    tm_wait(k);
+    const double om = 1 - al;
+    const double zhA = al * ax + om * ts.zA, zhB = al * xt + om * ts.zB;
+    const double znA = dmin(dmax(zhA + ts.yA * k.get(3), k.get(0)), k.get(1));
+    const double znB = dmin(dmax(zhB + ts.yB * k.get(7), k.get(4)), k.get(5));
+    ts.x = al * xt + om * ts.x;
+    ts.yA += k.get(2) * (zhA - znA);
+    ts.yB += k.get(6) * (zhB - znB);
+    ts.zA = znA; ts.zB = znB;
+    if (tid < SH::NA) c.w[tid] = k.get(2) * znA - ts.yA;
+#else
     if (var) xt = c.xt[i];
     tm_wait(k);
     if (tid < SH::NA) {
@@ -713,6 +724,7 @@ MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
         ts.yB += k.get(6) * (zh - zn);
         ts.zB = zn;
     }
+#endif
 }
 // ---- residual test (every check_termination iterations) ----------------------------------------------------------------
 template <class SH>
@@ -826,7 +838,7 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
         MPCB_WSTAMP(15)
         MPCB_APHASE_NS(a_rhs(c, ts, tid));
         MPCB_PRE_DECL(TmBuf<16>, wch0)
-        MPCB_APHASE({ a_rhs_p(c, tid); MPCB_PRE(if constexpr (PRE_B) w_prefetch(ts, tid, wch0)); MPCB_WSTAMP(0) });
+        MPCB_APHASE({ p_partial<SH>(tid, 14, c.pcv, c.w, c.psum); MPCB_PRE(if constexpr (PRE_B) w_prefetch(ts, tid, wch0)); MPCB_WSTAMP(0) });
         MPCB_PROF(1)
         // t = W rhs_I, published in the x~ slots of the interior variables (phase D overwrites them with x~_I = t - F x~_B)
         MPCB_APHASE_NS((b_w<SH, MPCB_PRE_ON && PRE_B>(c, ts, tid, wch0)));
@@ -835,7 +847,7 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
             const WRole r = wrole<SH>(tid);
             ts.t = ts.acc;
             if (r.valid && r.half == 0) c.xt[r.out] = ts.t;
-            b_w_p(c, tid);
+            p_partial<SH>(tid, MPCB_PW, c.fpc, c.rhs, c.psum + 32);
             MPCB_WSTAMP(1)
         });
         MPCB_PROF(2)

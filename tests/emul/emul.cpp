@@ -131,7 +131,7 @@ int emul_kkt_apply(const mpcb_settings* st, const mpcb_limits* lim, const double
     }
     c.sc[0] = 0;        // no A^T w gather in this test: rhs is given directly
     MPCB_PHASE_NS({ TmBuf<16> wch0; b_w<SH, false>(c, ts, tid, wch0); });
-    MPCB_PHASE({ MPCB_WREDUCE_EMUL() const WRole r = wrole<SH>(tid); ts.t = ts.acc; if (r.valid && r.half == 0) c.xt[r.out] = ts.t; b_w_p(c, tid); });
+    MPCB_PHASE({ MPCB_WREDUCE_EMUL() const WRole r = wrole<SH>(tid); ts.t = ts.acc; if (r.valid && r.half == 0) c.xt[r.out] = ts.t; p_partial<SH>(tid, MPCB_PW, c.fpc, c.rhs, c.psum + 32); });
     for (int j = 0; j < 32; j++) c.psum[j] = 0;        // no A^T w gather in this test
     MPCB_PHASE_NS(b_sbi(c, ts, tid));
     MPCB_PHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });

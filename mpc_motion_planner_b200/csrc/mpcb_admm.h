@@ -79,6 +79,18 @@ struct AL {
     static constexpr int R_LAM = SH::VP, R_INFO = SH::VP + SH::NDUAL + 4;
     static constexpr int QPBLOCK = G_RES + R_INFO + 4;
 
+    // row role: thread tid owns constraint row rowof(tid).  The inequality rows start on a warp boundary (thread 256): a warp that mixed
+    // equality and inequality rows would run both branches of the row product one after the other and be the last one of phase E.
+#ifndef MPCB_ROW_ALIGN
+#define MPCB_ROW_ALIGN 1
+#endif
+    static constexpr int ROW_GAP = MPCB_ROW_ALIGN ? (32 - SH::NEQ % 32) % 32 : 0;
+    MPCB_HD static int rowof(int tid) {
+        if (tid < SH::NEQ) return tid;
+        const int r = tid - ROW_GAP;
+        return (r >= SH::NEQ && r < SH::NA) ? r : -1;
+    }
+    MPCB_HD static int rtid(int r) { return r < SH::NEQ ? r : r + ROW_GAP; }
     MPCB_HD static int vidx(int k, int comp) { const int s = k / 3 > 5 ? 5 : k / 3; return SEG * s + 21 * (k - 3 * s) + comp; }
     MPCB_HD static int sepidx(int b) { return b < 70 ? SEG * (b / 14 + 1) + b % 14 : IP; }
     MPCB_HD static int ibase(int s) { return s == 0 ? 0 : SEG * s + 14; }                        // first interior index of segment s
@@ -689,7 +701,8 @@ MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     TmBuf<8> k;                                  // l, u, rho, 1/rho | lb, ub, rho_b, 1/rho_b
     tm_ld(ts.tma(), L::TM_CST, k);
     double ax = 0, xt = 0;
-    if (tid < SH::NA) ax = row_times(c, tid, c.xt);
+    const int row = L::rowof(tid);
+    if (row >= 0) ax = row_times(c, row, c.xt);
     int i, kk, comp;
     const bool var = vrole<SH>(tid, i, kk, comp);
 #if MPCB_EFLAT
@@ -706,16 +719,16 @@ MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     ts.yA += k.get(2) * (zhA - znA);
     ts.yB += k.get(6) * (zhB - znB);
     ts.zA = znA; ts.zB = znB;
-    if (tid < SH::NA) c.w[tid] = k.get(2) * znA - ts.yA;
+    if (row >= 0) c.w[row] = k.get(2) * znA - ts.yA;
 #else
     if (var) xt = c.xt[i];
     tm_wait(k);
-    if (tid < SH::NA) {
+    if (row >= 0) {
         const double zh = al * ax + (1 - al) * ts.zA;
         const double zn = dmin(dmax(zh + ts.yA * k.get(3), k.get(0)), k.get(1));
         ts.yA += k.get(2) * (zh - zn);
         ts.zA = zn;
-        c.w[tid] = k.get(2) * ts.zA - ts.yA;
+        c.w[row] = k.get(2) * ts.zA - ts.yA;
     }
     if (var) {
         ts.x = al * xt + (1 - al) * ts.x;
@@ -730,8 +743,9 @@ MPCB_DEV void e_update(ACtx<SH>& c, ATS<SH>& ts, int tid) {
 template <class SH>
 MPCB_DEV void chk_a(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
-    if (tid < SH::NA) c.rhs[tid] = ts.yA;       // the rhs slot is free until the next phase A
-    else if (tid < 416) c.rhs[tid] = 0;
+    const int row = L::rowof(tid);
+    if (row >= 0) c.rhs[row] = ts.yA;           // the rhs slot is free until the next phase A
+    if (tid >= SH::NA && tid < 416) c.rhs[tid] = 0;
     int i, k, comp;
     if (vrole<SH>(tid, i, k, comp)) c.xt[i] = ts.x;
 }
@@ -739,8 +753,9 @@ template <class SH>
 MPCB_DEV void chk_b(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     typedef AL<SH> L;
     double rp = 0, nax = 0, nz = 0, nx = 0, rd = 0, nhx = 0, naty = 0;
-    if (tid < SH::NA) {
-        const double ax = row_times(c, tid, c.xt);
+    const int row = L::rowof(tid);
+    if (row >= 0) {
+        const double ax = row_times(c, row, c.xt);
         rp = fabs(ax - ts.zA); nax = fabs(ax); nz = fabs(ts.zA);
     }
     int i, k, comp;
@@ -783,7 +798,7 @@ template <class SH>
 MPCB_DEV void a_finish(ACtx<SH>& c, ATS<SH>& ts, int tid, int max_iter) {
     typedef AL<SH> L;
     double* res = c.g + L::G_RES;
-    if (tid < SH::NA) res[L::R_LAM + tid] = ts.yA;
+    if (L::rowof(tid) >= 0) res[L::R_LAM + L::rowof(tid)] = ts.yA;
     int i, k, comp;
     if (vrole<SH>(tid, i, k, comp)) {
         const int io = (k < 0) ? SH::IP : SH::kvar(k, comp);

@@ -84,7 +84,7 @@ MPCB_DEV void exp_vec(const Ctx<SH>& c, const TS<SH>& ts, int tid, double* qb) {
     }
     {   // constants of ADMM threads that own no row / no variable
         int i, k, comp;
-        if (tid >= SH::NA) { tm[(L::TM_CST + 0) * NT + tid] = 0; tm[(L::TM_CST + 1) * NT + tid] = 0; tm[(L::TM_CST + 2) * NT + tid] = 1; tm[(L::TM_CST + 3) * NT + tid] = 1; }
+        if (L::rowof(tid) < 0) { tm[(L::TM_CST + 0) * NT + tid] = 0; tm[(L::TM_CST + 1) * NT + tid] = 0; tm[(L::TM_CST + 2) * NT + tid] = 1; tm[(L::TM_CST + 3) * NT + tid] = 1; }
         if (!vrole<SH>(tid, i, k, comp)) { tm[(L::TM_CST + 4) * NT + tid] = 0; tm[(L::TM_CST + 5) * NT + tid] = 0; tm[(L::TM_CST + 6) * NT + tid] = 1; tm[(L::TM_CST + 7) * NT + tid] = 1; }
     }
     if (tid < SH::NVAR) {                     // thread tid owns variable tid (kernel order); its ADMM thread is the padded-node-order index
@@ -94,9 +94,10 @@ MPCB_DEV void exp_vec(const Ctx<SH>& c, const TS<SH>& ts, int tid, double* qb) {
         tm[(L::TM_CST + 4) * NT + at] = ts.lb; tm[(L::TM_CST + 5) * NT + at] = ts.ub;
         tm[(L::TM_CST + 6) * NT + at] = ts.rhoB; tm[(L::TM_CST + 7) * NT + at] = 1.0 / ts.rhoB;
     }
-    if (tid < SH::NA) {
-        tm[(L::TM_CST + 0) * NT + tid] = ts.l; tm[(L::TM_CST + 1) * NT + tid] = ts.u;
-        tm[(L::TM_CST + 2) * NT + tid] = ts.rho; tm[(L::TM_CST + 3) * NT + tid] = 1.0 / ts.rho;
+    if (tid < SH::NA) {                       // thread tid owns row tid; its ADMM thread is rtid(tid)
+        const int at = L::rtid(tid);
+        tm[(L::TM_CST + 0) * NT + at] = ts.l; tm[(L::TM_CST + 1) * NT + at] = ts.u;
+        tm[(L::TM_CST + 2) * NT + at] = ts.rho; tm[(L::TM_CST + 3) * NT + at] = 1.0 / ts.rho;
     }
     if (tid < 256) img[L::I_PCOL + tid] = (tid < SH::NEQ) ? c.pcol[tid] : 0.0;
     if (tid < 416) {

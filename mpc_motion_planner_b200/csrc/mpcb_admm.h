@@ -275,13 +275,14 @@ constexpr int ANT = MPCB_ADMM_WIDE ? NT : NT / 2;
 // Prefetch of thread-private constant operands (tensor memory) across the barrier that ends the previous phase: the device issues
 // the load before the barrier and hands the buffer to the consumer; the lock-step host emulation (one thread at a time, a phase
 // at a time) declares the buffer inside the consuming phase and loads it there (same values: the strips are constant during a QP).
-// which phases prefetch (device): bit 0 = first W overflow chunk (phase B).  The same for C^-1 (phase C), the F row (phase D) and the
-// row / box constants (phase E) was measured and is NOT done: holding their 16..36 destination registers across the barrier pushes the
-// 128-register kernel into spills (30.8 k -> 27.9 k OCP/s with D or E, 21.9 k with C)
+// Which phases prefetch (device): bit 0 = first W overflow chunk (phase B), bit 4 = the inequality-Jacobian column of phase A (a_fetch).
+// Measured and NOT done: C^-1 (phase C), the F row (D), the row / box constants (E) -- no gain, the
+// tensor-memory latency is not what bounds those intervals; the collocation coefficients of phase A and part of the inequality row
+// of phase E -- their 14..24 extra live registers cost more in spills than the shorter request burst gains (33.7 k -> 32.7 k / 33.0 k).
 #ifndef MPCB_PRE_MASK
-#define MPCB_PRE_MASK 1
+#define MPCB_PRE_MASK 17
 #endif
-constexpr bool PRE_B = MPCB_PRE_MASK & 1;
+constexpr bool PRE_B = MPCB_PRE_MASK & 1, PRE_A = MPCB_PRE_MASK & 16;
 #ifdef MPCB_EMUL
 #define MPCB_PRE_ON false
 #define MPCB_PRE_DECL(type, name) type name;
@@ -465,8 +466,21 @@ MPCB_DEV void p_partial(int tid, int w, const double* a, const double* b, double
 // ---- phase A: rhs = sigma x - h + rho_b z_b - y_b + A^T w  (the p entry of A^T w is added in phase C, see b_sbi) ----
 // Straight-line (branch-free) so that the compiler can interleave the loads of the two logical threads a physical thread
 // runs: conditions become zero coefficients (dt[20] holds 0.0) and clamped addresses, the store is predicated.
+// the 8 inequality-Jacobian coefficients of the thread's variable (its column of the node's 8 x 22 block, transposed copy): constant
+// during a QP.  On the device they are read BEFORE the barrier that precedes phase A (end of phase E / of the residual test), so that
+// the burst of shared-memory requests behind that barrier is shorter (a_fetch is unconditional: every thread has a valid address).
+struct AGt { d2 ga, gb, gc, gd; };
 template <class SH>
-MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid) {
+MPCB_DEV void a_fetch(const ACtx<SH>& c, int tid, AGt& q) {
+    typedef AL<SH> L;
+    const int ii = tid < L::IP ? tid : 0;
+    const int s = (ii / L::SEG) > 5 ? 5 : (ii / L::SEG), rem = ii - L::SEG * s;
+    const int j = rem / 21, comp = rem - 21 * j, k = 3 * s + j;
+    const double* G = c.Gt + k * L::GTS + comp * L::GTC;
+    q.ga = ld2(G); q.gb = ld2(G + 2); q.gc = ld2(G + 4); q.gd = ld2(G + 6);
+}
+template <class SH, bool PRE>
+MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid, AGt& q) {
     typedef AL<SH> L;
     if (tid >= L::PTID + 32) return;                  // warps 14, 15 own no variable (warp-uniform)
     const bool isp = tid == L::PTID;
@@ -482,12 +496,12 @@ MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     const double* yy1 = y + 42 * (c1 ? s1 : 0) + cc;
     const double* yy2 = y + 42 * (c2 ? s1 - 1 : 0) + cc;
     const double* y3 = y + (c3 ? 14 * k + comp - 7 : 0);
+    const double* yi = y + SH::NEQ + 8 * k;
+    if constexpr (!PRE) a_fetch<SH>(c, tid, q);
     const double d10 = c.dt[c1 ? l1 : Z], d11 = c.dt[c1 ? 4 + l1 : Z], d12 = c.dt[c1 ? 8 + l1 : Z];
     const double d20 = c.dt[c2 ? 3 : Z], d21 = c.dt[c2 ? 7 : Z], d22 = c.dt[c2 ? 11 : Z];
     const double mt = c.dt[c3 ? 16 : Z];
-    const double* G = c.Gt + k * L::GTS + comp * L::GTC;
-    const double* yi = y + SH::NEQ + 8 * k;
-    const d2 ga = ld2(G), gb = ld2(G + 2), gc = ld2(G + 4), gd = ld2(G + 6);
+    const d2 ga = q.ga, gb = q.gb, gc = q.gc, gd = q.gd;
     const d2 va = ld2(yi), vb = ld2(yi + 2), vc = ld2(yi + 4), vd = ld2(yi + 6);
     double g0 = 0, g1 = 0, g2 = 0, g3 = 0;
     g0 += d10 * yy1[0]; g1 += d11 * yy1[14]; g2 += d12 * yy1[28];
@@ -847,11 +861,13 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
     MPCB_PROF_DECL
     MPCB_APHASE(a_load(c, ts, tid));
     MPCB_PROF(0)
+    MPCB_PRE_DECL(AGt, agt)
+    MPCB_APHASE_NS({ MPCB_PRE(if constexpr (PRE_A) a_fetch<SH>(c, tid, agt)); });
     const int max_iter = c.st->qp_max_iter, chk = c.st->qp_check_termination;
     int until_chk = chk > 0 ? chk : -1;          // iterations left until the next residual test (a countdown: no integer division per iteration)
     for (int iter = 1; iter <= max_iter; iter++) {
         MPCB_WSTAMP(15)
-        MPCB_APHASE_NS(a_rhs(c, ts, tid));
+        MPCB_APHASE_NS((a_rhs<SH, MPCB_PRE_ON && PRE_A>(c, ts, tid, agt)));
         MPCB_PRE_DECL(TmBuf<16>, wch0)
         MPCB_APHASE({ p_partial<SH>(tid, 14, c.pcv, c.w, c.psum); MPCB_PRE(if constexpr (PRE_B) w_prefetch(ts, tid, wch0)); MPCB_WSTAMP(0) });
         MPCB_PROF(1)
@@ -892,7 +908,7 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
             MPCB_WSTAMP(4)
         });
         MPCB_PROF(5)
-        MPCB_APHASE({ e_update(c, ts, tid); MPCB_WSTAMP(5) });
+        MPCB_APHASE({ e_update(c, ts, tid); MPCB_PRE(if constexpr (PRE_A) a_fetch<SH>(c, tid, agt)); MPCB_WSTAMP(5) });
         MPCB_WSTAMP(6)
         MPCB_PROF(6)
         if (--until_chk == 0) {

@@ -114,6 +114,9 @@ node_val_kernel(const int n, const int ntrial, const double tau, double* __restr
     for (int j = 0; j < 8; j++) ws[WS<SH>::GVAL + (t * SH::NN + k) * 8 + j] = g[j];
 }
 
+#ifndef MPCB_SMEM_OPAQUE
+#define MPCB_SMEM_OPAQUE 1
+#endif
 // the hot kernel: <= qp_max_iter box-ADMM iterations of one QP per CTA at a time
 template <class SH>
 __global__ void __launch_bounds__(ANT, 1)
@@ -123,7 +126,16 @@ admm_kernel(const __grid_constant__ KernelConst kc, const int n, int* __restrict
     __shared__ uint32_t s_tmem;
     const int ptid = threadIdx.x;       // physical thread: runs the logical threads ptid and ptid + ANT (mpcb_admm.h)
     ACtx<SH> c;
+#if MPCB_SMEM_OPAQUE
+    // the base of the dynamic shared memory as an opaque register value that is still known to be a shared-memory address: otherwise the
+    // compiler re-derives it at every phase (S2UR SR_CgaCtaId + LEA + IMAD in front of the first load behind each barrier)
+    double* sbase = smem;
+    asm volatile("" : "+l"(sbase));
+    __builtin_assume(__isShared(sbase));
+    c.bind(sbase);
+#else
     c.bind(smem);
+#endif
     c.st = &kc.st;
     c.prof = prof;
     ATS<SH> ts0, ts1;

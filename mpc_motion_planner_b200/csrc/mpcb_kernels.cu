@@ -46,6 +46,9 @@ __device__ __forceinline__ void bind_problem(Ctx<SH>& c, Problem& pb, const Kern
 // factorise and the ADMM iterations in one kernel: larger collocation shapes, adaptive rho).  gmat: one matrix block per CTA for the
 // shapes whose KKT inverses do not fit shared memory (Layout::GMAT).
 // GEN selects the kernel that holds kind 3 only, so that the code generation of the three light stages does not change with it.
+#ifndef MPCB_STAGE_SMEM_OPAQUE
+#define MPCB_STAGE_SMEM_OPAQUE 1
+#endif
 template <class SH, bool GEN>
 __global__ void __launch_bounds__(SH::NT, 1)
 sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, const int n, const int kind, const int it,
@@ -56,7 +59,14 @@ sqp_stage_kernel(const __grid_constant__ KernelConst kc, const BatchPtrs bp, con
     extern __shared__ double smem[];
     const int tid = threadIdx.x;
     Ctx<SH> c;
+#if MPCB_STAGE_SMEM_OPAQUE
+    double* sbase = smem;                  // as in admm_kernel: the shared base held in a register instead of re-derived per phase
+    asm volatile("" : "+l"(sbase));
+    __builtin_assume(__isShared(sbase));
+    c.bind(sbase, gmat + (size_t)blockIdx.x * Layout<SH>::CTA_BLOCK);
+#else
     c.bind(smem, gmat + (size_t)blockIdx.x * Layout<SH>::CTA_BLOCK);
+#endif
     volatile long long& s_next = *reinterpret_cast<volatile long long*>(c.isc + IS_NEXT);
     c.st = &kc.st;
     c.cheb = &kc.cheb;

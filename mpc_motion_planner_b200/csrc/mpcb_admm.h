@@ -217,7 +217,13 @@ struct ACtx {
         umax = reinterpret_cast<unsigned long long*>(sm + L::V_UMAX);
         isc = reinterpret_cast<long long*>(sm + L::V_ISC);
     }
-    MPCB_HD double D(int j, int l) const { return dt[4 * j + l]; }
+    // collocation differentiation matrix: from the constant bank (a separate path from the shared-memory pipe that bounds phases A and E)
+    // or from the shared-memory image (MPCB_DCONST 0)
+#ifndef MPCB_DCONST
+#define MPCB_DCONST 1
+#endif
+    const ChebConst* cheb;
+    MPCB_HD double D(int j, int l) const { return MPCB_DCONST ? cheb->D[j][l] : dt[4 * j + l]; }
     MPCB_HD double mtp() const { return dt[16]; }
 };
 
@@ -498,9 +504,15 @@ MPCB_DEV void a_rhs(ACtx<SH>& c, ATS<SH>& ts, int tid, AGt& q) {
     const double* y3 = y + (c3 ? 14 * k + comp - 7 : 0);
     const double* yi = y + SH::NEQ + 8 * k;
     if constexpr (!PRE) a_fetch<SH>(c, tid, q);
+#if MPCB_DCONST
+    const double d10 = c1 ? c.cheb->D[0][l1] : 0.0, d11 = c1 ? c.cheb->D[1][l1] : 0.0, d12 = c1 ? c.cheb->D[2][l1] : 0.0;
+    const double d20 = c2 ? c.cheb->D[0][3] : 0.0, d21 = c2 ? c.cheb->D[1][3] : 0.0, d22 = c2 ? c.cheb->D[2][3] : 0.0;
+    const double mt = c.dt[c3 ? 16 : Z];
+#else
     const double d10 = c.dt[c1 ? l1 : Z], d11 = c.dt[c1 ? 4 + l1 : Z], d12 = c.dt[c1 ? 8 + l1 : Z];
     const double d20 = c.dt[c2 ? 3 : Z], d21 = c.dt[c2 ? 7 : Z], d22 = c.dt[c2 ? 11 : Z];
     const double mt = c.dt[c3 ? 16 : Z];
+#endif
     const d2 ga = q.ga, gb = q.gb, gc = q.gc, gd = q.gd;
     const d2 va = ld2(yi), vb = ld2(yi + 2), vc = ld2(yi + 4), vd = ld2(yi + 6);
     double g0 = 0, g1 = 0, g2 = 0, g3 = 0;

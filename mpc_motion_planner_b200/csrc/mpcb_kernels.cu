@@ -147,6 +147,7 @@ admm_kernel(const __grid_constant__ KernelConst kc, const int n, int* __restrict
     c.bind(smem);
 #endif
     c.st = &kc.st;
+    c.cheb = &kc.cheb;
     c.prof = prof;
     ATS<SH> ts0, ts1;
     // all 512 TMEM columns of the SM for this CTA (one CTA per SM): thread-private operand strips, mpcb_tmem.h

@@ -36,7 +36,7 @@ struct Emu {
             asmem.assign(AL<SH>::TOTAL, 0.0);
             atsv.resize(NT);
             ac.bind(asmem.data());
-            ac.st = st; ac.g = qb.data();
+            ac.st = st; ac.cheb = &cheb; ac.g = qb.data();
             std::memset(atsv.data(), 0, sizeof(ATS<SH>) * NT);
         }
         std::memset(tsv.data(), 0, sizeof(TS<SH>) * SH::NT);

@@ -338,9 +338,13 @@ MPCB_DEV double row_times(const ACtx<SH>& c, int r, const double* x) {
     const double* xs = x + (L::vidx(k, 0) & ~1);
     double a0 = 0, a1 = 0, a2 = 0, a3 = c.pcv[r] * x[L::IP];
     MPCB_UNROLL
-    for (int cc = 0; cc < 24; cc += 4) {
+    for (int cc = 0; cc < 20; cc += 4) {
         const d2 g = ld2(G + cc), g2 = ld2(G + cc + 2), v = ld2(xs + cc), v2 = ld2(xs + cc + 2);
         a0 += g.a * v.a; a1 += g.b * v.b; a2 += g2.a * v2.a; a3 += g2.b * v2.b;
+    }
+    {   // slots 20, 21 (the 21 coefficients sit in slots shift .. shift + 20, shift <= 1); 22 .. 25 are pads
+        const d2 g = ld2(G + 20), v = ld2(xs + 20);
+        a0 += g.a * v.a; a1 += g.b * v.b;
     }
     return (a0 + a1) + (a2 + a3);
 }

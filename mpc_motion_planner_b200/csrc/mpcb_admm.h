@@ -207,6 +207,7 @@ struct ACtx {
     double* g;                     // this OCP's QP block in global memory
     const mpcb_settings* st;
     long long* prof;               // MPCB_PROFILE builds: per-phase cycle counters of CTA 0 (else unused)
+    int dbg_iter;                  // MPCB_PROFILE builds: the iteration counter, for time stamps inside the phase functions
     MPCB_HD void bind(double* smem) {
         typedef AL<SH> L;
         sm = smem;
@@ -564,6 +565,12 @@ MPCB_DEV void w_slots(const double* x, const COEF& coef, double* acc) {
     MPCB_UNROLL
     for (int e = E0; e < (E1 < R * STEPS ? E1 : R * STEPS); e++) acc[e % R] += coef(e) * x[e / R];
 }
+// MPCB_PROFILE builds: time stamp `slot` (7..14) of the thread's warp inside a phase function, iteration 100 of CTA 0
+#if defined(MPCB_PROFILE) && !defined(MPCB_EMUL)
+#define MPCB_ISTAMP(slot) if (c.dbg_iter == 100 && blockIdx.x == 0 && c.prof && (tid & 31) == 0) c.prof[64 + 16 * (slot) + (tid >> 5)] = clock64();
+#else
+#define MPCB_ISTAMP(slot)
+#endif
 // one thread's R x STEPS block of W times the vector.  The first TMEM overflow chunk (16 slots) arrives in `pre`: on the device it
 // is loaded BEFORE the barrier that ends phase A (w_prefetch: thread-private constant data, so the barrier wait hides the tensor-memory
 // latency); the host emulation loads it here.  Order: chunk 0 | second chunk requested | register coefficients (cover its latency) |
@@ -578,16 +585,21 @@ MPCB_DEV void w_block(ACtx<SH>& c, ATS<SH>& ts, int tid, const double* b, double
     MPCB_UNROLL
     for (int t = 0; t < STEPS; t++) x[t] = b[8 * t];
     tm_wait(ch0);
+    MPCB_ISTAMP(7)
     w_slots<R, STEPS, W, W + 16>(x, [&](int e) { return ch0.get(e - W); }, acc);
+    MPCB_ISTAMP(8)
     if constexpr (NCH > 1) {
         TmBuf<16> ch1;
         tm_ld_after(ts.tma(), L::tm_wov(tid) + 16, ch1, x);
         w_slots<R, STEPS, 0, W>(x, [&](int e) { return ts.wreg[e]; }, acc);
+        MPCB_ISTAMP(9)
         tm_wait(ch1);
         w_slots<R, STEPS, W + 16, W + 32>(x, [&](int e) { return ch1.get(e - W - 16); }, acc);
     } else {
         w_slots<R, STEPS, 0, W>(x, [&](int e) { return ts.wreg[e]; }, acc);
+        MPCB_ISTAMP(9)
     }
+    MPCB_ISTAMP(10)
 }
 // device: request the first overflow chunk of the thread's W block (every kind has one, at the same strip offset)
 template <class SH>
@@ -890,6 +902,9 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
     const int max_iter = c.st->qp_max_iter, chk = c.st->qp_check_termination;
     int until_chk = chk > 0 ? chk : -1;          // iterations left until the next residual test (a countdown: no integer division per iteration)
     for (int iter = 1; iter <= max_iter; iter++) {
+#if defined(MPCB_PROFILE) && !defined(MPCB_EMUL)
+        c.dbg_iter = iter;
+#endif
         MPCB_WSTAMP(15)
         MPCB_APHASE_NS((a_rhs<SH, MPCB_PRE_ON && PRE_A>(c, ts, tid, agt)));
         MPCB_PRE_DECL(TmBuf<16>, wch0)

@@ -621,6 +621,7 @@ MPCB_DEV void b_w(ACtx<SH>& c, ATS<SH>& ts, int tid, TmBuf<16>& ch0) {
     for (int i = 0; i < 8; i++) ts.pv[i] = v[i];
 #else
     ts.acc = r.kind == 1 ? wreduce<8>(v, r.q) : wreduce<4>(v, r.q);
+    MPCB_ISTAMP(11)
 #endif
 }
 // ---- phase B': separator right-hand side r_B = rhs_B - S_BI t (4 lanes per junction variable), r_B[p] -------------------------

@@ -465,6 +465,29 @@ def run_ours(args):
     rh.sort()
     line["stats"]["receding_horizon"] = {"batch": RB, "resolves": len(rh), "p50_ms": rh[len(rh) // 2], "p99_ms": rh[min(len(rh) - 1, int(0.99 * len(rh)))],
                                          "note": "x0 advanced by 1 ms along the previous solution before every re-solve; warm start from the previous solution and multipliers"}
+    # the same batch with the library's opt-in splitting over internal streams (MPCB_PARTS = 4: the persistent kernels of one part fill the
+    # idle SMs of another part's last wave); informational, the headline figures above come from the default single-stream path
+    if "MPCB_PARTS" not in os.environ:
+        os.environ["MPCB_PARTS"] = "4"
+        try:
+            sv4 = M.Solver(s, lim, device=local)
+            t4 = []
+            for i in range(5):
+                a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+                flush.fill_(1)
+                a.record()
+                sv4.solve_device(B, dx0.data_ptr(), dxT.data_ptr(), dgx.data_ptr(), dgu.data_ptr(), dgT.data_ptr(), 0, dsx.data_ptr(), dsu.data_ptr(),
+                                 dsT.data_ptr(), 0, dst.data_ptr(), stream)
+                b.record(); torch.cuda.synchronize()
+                if i >= 2:
+                    t4.append(a.elapsed_time(b))
+            t4.sort()
+            line["stats"]["split_over_4_internal_streams"] = {"ms_per_step": t4[len(t4) // 2], "value": B / (t4[len(t4) // 2] * 1e-3), "unit": UNIT,
+                                                              "note": "MPCB_PARTS=4, this rank's batch, device-resident; opt-in (see INTEGRATION.md)"}
+            sv4.close()
+        except Exception as e:        # informational only
+            line["stats"]["split_over_4_internal_streams"] = {"error": str(e)[:200]}
+        del os.environ["MPCB_PARTS"]
     if world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         n_sample = min(B, max(threads * 320, 640)) if not base_shape else max(threads * 320, 640)      # about 10 s of CPU work on all host threads

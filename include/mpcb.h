@@ -119,6 +119,8 @@ int mpcb_set_limits(mpcb_handle* h, const mpcb_limits* lim);
  *   mem         MPCB_MEM_HOST: plain host pointers, copies are made inside the call (synchronous);
  *               MPCB_MEM_DEVICE: device pointers on the handle's device, the call only enqueues work on `stream`
  *   stream      cudaStream_t (NULL = default stream)
+ * Environment (read by mpcb_create): MPCB_PARTS = 2..4 lets the call split every chunk of at least two waves of CTAs over internal
+ * streams of the handle (fork / join with events behind `stream`); default 1 = off.
  */
 int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, const double* guess_x,
                      const double* guess_u, const double* guess_T, const double* guess_lam, double* sol_x,

@@ -5,7 +5,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "mpcb.h"
@@ -41,6 +43,13 @@ struct mpcb_handle {
     // workspace, counters and staging buffers are per handle, not per stream)
     cudaEvent_t ev_last = nullptr;
     cudaStream_t last_stream = nullptr;
+    // a chunk of at least two waves is solved as up to MAX_PARTS parts on the caller's stream and on internal streams: the persistent
+    // kernels of one part leave SMs idle in their last wave, the kernels of the other parts fill them (each part has its own work
+    // counters, workspace slice and matrix blocks; fork / join with events, so the call still looks like work on one stream)
+    static const int MAX_PARTS = 4;
+    int parts = 1;
+    cudaStream_t aux[MAX_PARTS - 1] = {nullptr, nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join[MAX_PARTS - 1] = {nullptr, nullptr, nullptr};
     bool busy = false;
     bool timed = false;
     cudaStream_t timed_stream = nullptr;
@@ -102,7 +111,21 @@ int mpcb_create(const mpcb_settings* s, int device, mpcb_handle** out) {
     }
     if ((e = solve_prepare(s->poly_order, s->num_seg)) != cudaSuccess) return fail("cudaFuncSetAttribute(solve kernels)", e);
     h->grid_max = h->sm_count;      // one CTA per SM (shared memory bound)
-    if (h->si.gmat_doubles && (e = cudaMalloc(&h->d_gmat, sizeof(double) * h->si.gmat_doubles * (size_t)h->grid_max)) != cudaSuccess) return fail("cudaMalloc(matrix blocks)", e);
+    {
+        // MPCB_PARTS = 2..4 switches the splitting on (+2.5 % OCP/s on 1000 problems, profiles/r2zb_parts.txt).  Off by default: with
+        // overlapping kernels the per-kernel times of mpcb_last_kernel_ms (start-to-end spans, which then include the wait for a free SM)
+        // no longer measure a kernel that has the GPU to itself, which is what the roofline of bench.py is defined on.
+        const char* pe = getenv("MPCB_PARTS");
+        h->parts = pe ? atoi(pe) : 1;
+        if (h->parts < 1) h->parts = 1;
+        if (h->parts > mpcb_handle::MAX_PARTS) h->parts = mpcb_handle::MAX_PARTS;
+        for (int i = 0; i + 1 < h->parts; i++) {
+            if ((e = cudaStreamCreateWithFlags(&h->aux[i], cudaStreamNonBlocking)) != cudaSuccess) return fail("cudaStreamCreate", e);
+            if ((e = cudaEventCreateWithFlags(&h->ev_join[i], cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+        }
+        if ((e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
+    }
+    if (h->si.gmat_doubles && (e = cudaMalloc(&h->d_gmat, sizeof(double) * h->si.gmat_doubles * (size_t)h->grid_max * h->parts)) != cudaSuccess) return fail("cudaMalloc(matrix blocks)", e);
     if ((e = cudaMalloc(&h->d_prof, 512 * sizeof(long long))) != cudaSuccess || (e = cudaMemset(h->d_prof, 0, 512 * sizeof(long long))) != cudaSuccess) return fail("cudaMalloc(prof)", e);
     if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess || (e = cudaEventCreate(&h->ev1)) != cudaSuccess ||
         (e = cudaEventCreateWithFlags(&h->ev_last, cudaEventDisableTiming)) != cudaSuccess) return fail("cudaEventCreate", e);
@@ -122,6 +145,11 @@ void mpcb_destroy(mpcb_handle* h) {
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     if (h->ev_last) cudaEventDestroy(h->ev_last);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    for (int i = 0; i < mpcb_handle::MAX_PARTS - 1; i++) {
+        if (h->ev_join[i]) cudaEventDestroy(h->ev_join[i]);
+        if (h->aux[i]) cudaStreamDestroy(h->aux[i]);
+    }
     delete h;
 }
 
@@ -234,49 +262,91 @@ int mpcb_solve_batch(mpcb_handle* h, int n, const double* x0, const double* xT, 
         bp.sx = dsx; bp.su = dsu; bp.sT = dsT; bp.slam = dsl; bp.stats = dst;
     }
     const int chunk = n < CHUNK_MAX ? n : CHUNK_MAX;
-    const int n_launch = 2 + 3 * h->st.sqp_max_iter;               // persistent kernels (one work counter each) per chunk
-    { int rc = ensure_workspace(h, chunk, n_launch); if (rc) return rc; }
+    const int n_launch = 2 + 3 * h->st.sqp_max_iter;               // persistent kernels (one work counter each) per part of a chunk
+    { int rc = ensure_workspace(h, chunk, n_launch * h->parts); if (rc) return rc; }
     h->kused = 0;
     const bool debug_sync = getenv("MPCB_DEBUG_SYNC") != nullptr;      // debugging aid: synchronise after every launch and name the failing kernel
     CK(cudaEventRecord(h->ev0, stream));
-#define TIMED(kind_, call_)                                                                                        \
+#define TIMED(s_, kind_, call_)                                                                                    \
     do {                                                                                                           \
-        if (timed_launch_begin(h, kind_, stream)) { h->err = "cudaEventRecord failed"; return MPCB_ERR_CUDA; }     \
+        if (timed_launch_begin(h, kind_, s_)) { h->err = "cudaEventRecord failed"; return MPCB_ERR_CUDA; }         \
         CK(call_);                                                                                                 \
-        timed_launch_end(h, stream);                                                                               \
+        timed_launch_end(h, s_);                                                                                   \
         if (debug_sync) {                                                                                          \
-            cudaError_t se_ = cudaStreamSynchronize(stream);                                                       \
+            cudaError_t se_ = cudaStreamSynchronize(s_);                                                           \
             if (se_ != cudaSuccess) {                                                                              \
                 h->err = std::string(#call_) + " [kernel]: " + cudaGetErrorString(se_);                            \
                 return MPCB_ERR_CUDA;                                                                              \
             }                                                                                                      \
         }                                                                                                          \
     } while (0)
+    struct Part { int nn, grid; BatchPtrs cp; int* ctr; double* ws; double* gm; cudaStream_t s; };
+    const bool generic = settings_generic_path(&h->st) != 0;
     for (int c0 = 0; c0 < n; c0 += chunk) {
         const int nn = (n - c0) < chunk ? (n - c0) : chunk;
-        const int grid = nn < h->grid_max ? nn : h->grid_max;
-        BatchPtrs cp = bp;
-        cp.x0 += (size_t)14 * c0; cp.xT += (size_t)14 * c0; cp.gx += (size_t)14 * N * c0; cp.gu += (size_t)7 * N * c0; cp.gT += c0;
-        if (cp.glam) cp.glam += (size_t)ND * c0;
-        cp.sx += (size_t)14 * N * c0; cp.su += (size_t)7 * N * c0; cp.sT += c0;
-        if (cp.slam) cp.slam += (size_t)ND * c0;
-        if (cp.stats) cp.stats += c0;
-        CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int) * n_launch, stream));
+        // parts of at least one wave each (a chunk below two waves stays whole: the latency path)
+        int P = (h->parts > 1 && nn >= 2 * h->grid_max) ? nn / h->grid_max : 1;
+        if (P > h->parts) P = h->parts;
+        Part part[mpcb_handle::MAX_PARTS];
+        for (int p = 0; p < P; p++) {
+            const int a = (int)((long long)nn * p / P), b = (int)((long long)nn * (p + 1) / P), o = c0 + a;
+            Part& pt = part[p];
+            pt.nn = b - a; pt.grid = pt.nn < h->grid_max ? pt.nn : h->grid_max;
+            pt.cp = bp;
+            pt.cp.x0 += (size_t)14 * o; pt.cp.xT += (size_t)14 * o; pt.cp.gx += (size_t)14 * N * o; pt.cp.gu += (size_t)7 * N * o; pt.cp.gT += o;
+            if (pt.cp.glam) pt.cp.glam += (size_t)ND * o;
+            pt.cp.sx += (size_t)14 * N * o; pt.cp.su += (size_t)7 * N * o; pt.cp.sT += o;
+            if (pt.cp.slam) pt.cp.slam += (size_t)ND * o;
+            if (pt.cp.stats) pt.cp.stats += o;
+            pt.ctr = h->d_counter + p * n_launch;
+            pt.ws = h->d_workspace + h->si.ws_doubles * (size_t)a;
+            pt.gm = h->d_gmat ? h->d_gmat + h->si.gmat_doubles * (size_t)h->grid_max * p : nullptr;
+            pt.s = p == 0 ? stream : h->aux[p - 1];
+        }
+        CK(cudaMemsetAsync(h->d_counter, 0, sizeof(int) * n_launch * P, stream));
+        if (P > 1) {
+            CK(cudaEventRecord(h->ev_fork, stream));
+            for (int p = 1; p < P; p++) CK(cudaStreamWaitEvent(part[p].s, h->ev_fork, 0));
+        }
         int li = 0;
-        // load -> [node Jacobians -> linearise/factorise -> ADMM -> node trial values -> line search/step] x sqp_max_iter
-        // (the shape-generic / adaptive-rho path runs linearise + factorise + ADMM as one kernel, accounted as the ADMM kind)
-        const bool generic = settings_generic_path(&h->st) != 0;
-        TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 0, 0, grid, h->d_counter + li++, h->d_workspace, h->d_gmat, h->d_prof, stream));
+        // load -> [node Jacobians -> linearise/factorise -> ADMM -> node trial values -> line search/step] x sqp_max_iter, stage by
+        // stage over the parts (the shape-generic / adaptive-rho path runs linearise + factorise + ADMM as one kernel, accounted as
+        // the ADMM kind)
+        for (int p = 0; p < P; p++) {
+            Part& pt = part[p];
+            TIMED(pt.s, MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, pt.cp, pt.nn, 0, 0, pt.grid, pt.ctr + li, pt.ws, pt.gm, h->d_prof, pt.s));
+        }
+        li++;
         for (int it = 1; it <= h->st.sqp_max_iter; it++) {
-            TIMED(MPCB_KERNEL_NODE, launch_node_jac(h->kc, nn, h->d_workspace, stream));
+            for (int p = 0; p < P; p++) { Part& pt = part[p]; TIMED(pt.s, MPCB_KERNEL_NODE, launch_node_jac(h->kc, pt.nn, pt.ws, pt.s)); }
             if (generic) {
-                TIMED(MPCB_KERNEL_ADMM, launch_sqp_stage(h->kc, cp, nn, 3, it, grid, h->d_counter + li++, h->d_workspace, h->d_gmat, h->d_prof, stream));
+                for (int p = 0; p < P; p++) {
+                    Part& pt = part[p];
+                    TIMED(pt.s, MPCB_KERNEL_ADMM, launch_sqp_stage(h->kc, pt.cp, pt.nn, 3, it, pt.grid, pt.ctr + li, pt.ws, pt.gm, h->d_prof, pt.s));
+                }
+                li++;
             } else {
-                TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 1, it, grid, h->d_counter + li++, h->d_workspace, h->d_gmat, h->d_prof, stream));
-                TIMED(MPCB_KERNEL_ADMM, launch_admm(h->kc, nn, grid, h->d_counter + li++, h->d_workspace, h->d_prof, stream));
+                for (int p = 0; p < P; p++) {
+                    Part& pt = part[p];
+                    TIMED(pt.s, MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, pt.cp, pt.nn, 1, it, pt.grid, pt.ctr + li, pt.ws, pt.gm, h->d_prof, pt.s));
+                }
+                li++;
+                for (int p = 0; p < P; p++) {
+                    Part& pt = part[p];
+                    TIMED(pt.s, MPCB_KERNEL_ADMM, launch_admm(h->kc, pt.nn, pt.grid, pt.ctr + li, pt.ws, h->d_prof, pt.s));
+                }
+                li++;
             }
-            TIMED(MPCB_KERNEL_NODE, launch_node_val(h->kc, nn, h->d_workspace, stream));
-            TIMED(MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, cp, nn, 2, it, grid, h->d_counter + li++, h->d_workspace, h->d_gmat, h->d_prof, stream));
+            for (int p = 0; p < P; p++) { Part& pt = part[p]; TIMED(pt.s, MPCB_KERNEL_NODE, launch_node_val(h->kc, pt.nn, pt.ws, pt.s)); }
+            for (int p = 0; p < P; p++) {
+                Part& pt = part[p];
+                TIMED(pt.s, MPCB_KERNEL_SQP_STAGE, launch_sqp_stage(h->kc, pt.cp, pt.nn, 2, it, pt.grid, pt.ctr + li, pt.ws, pt.gm, h->d_prof, pt.s));
+            }
+            li++;
+        }
+        for (int p = 1; p < P; p++) {
+            CK(cudaEventRecord(h->ev_join[p - 1], part[p].s));
+            CK(cudaStreamWaitEvent(stream, h->ev_join[p - 1], 0));
         }
     }
 #undef TIMED
@@ -519,13 +589,23 @@ double mpcb_last_kernel_ms(mpcb_handle* h, int kind) {
     if (!h || !h->timed) return -1.0;
     cudaSetDevice(h->device);
     if (cudaEventSynchronize(h->ev1) != cudaSuccess) return -1.0;
-    double total = 0;
+    // the launches of one kind may overlap (parts on different streams): the length of the UNION of their intervals, measured from the
+    // start event of the call (equal to the sum of the durations when nothing overlaps)
+    std::vector<std::pair<float, float>> iv;
     for (int i = 0; i < h->kused; i++) {
         if (h->kkind[i] != kind) continue;
-        float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, h->kev[2 * i], h->kev[2 * i + 1]) != cudaSuccess) return -1.0;
-        total += ms;
+        float a = 0.f, b = 0.f;
+        if (cudaEventElapsedTime(&a, h->ev0, h->kev[2 * i]) != cudaSuccess || cudaEventElapsedTime(&b, h->ev0, h->kev[2 * i + 1]) != cudaSuccess) return -1.0;
+        iv.push_back(std::make_pair(a, b));
     }
+    std::sort(iv.begin(), iv.end());
+    double total = 0;
+    float lo = 0.f, hi = -1.f;
+    for (size_t i = 0; i < iv.size(); i++) {
+        if (hi < lo || iv[i].first > hi) { if (hi >= lo) total += hi - lo; lo = iv[i].first; hi = iv[i].second; }
+        else if (iv[i].second > hi) hi = iv[i].second;
+    }
+    if (hi >= lo) total += hi - lo;
     return total;
 }
 int mpcb_debug_phase_cycles(mpcb_handle* h, long long* out32, int reset) {   // 512 slots: 0..31 phases, 64.. per-warp stamps

@@ -826,8 +826,7 @@ MPCB_DEV void chk_b(ACtx<SH>& c, ATS<SH>& ts, int tid) {
     }
     // the test only uses max(|Ax|, |x|, |z|) and max(|Hx|, |A^T y|): four warp reductions instead of seven (the slots UM_NZ, UM_NX
     // and UM_NATY stay zero)
-    umax_accum(c.umax + UM_RP, rp); umax_accum(c.umax + UM_NAX, dmax(dmax(nax, nz), nx));
-    umax_accum(c.umax + UM_RD, rd); umax_accum(c.umax + UM_NHX, dmax(nhx, naty));
+    umax_accum4(c.umax + UM_RP, rp, c.umax + UM_NAX, dmax(dmax(nax, nz), nx), c.umax + UM_RD, rd, c.umax + UM_NHX, dmax(nhx, naty));
 }
 template <class SH>
 MPCB_DEV void chk_c(ACtx<SH>& c, ATS<SH>& ts, int tid, int iter) {

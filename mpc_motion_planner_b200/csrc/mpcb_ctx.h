@@ -207,6 +207,23 @@ MPCB_DEV void umax_accum(unsigned long long* slot, double v) {
     if ((threadIdx.x & 31) == 0) atomicMax(slot, b);
 #endif
 }
+// four maxima at once: the four shuffle butterflies are independent, interleaved they cost the latency of one
+MPCB_DEV void umax_accum4(unsigned long long* s0, double v0, unsigned long long* s1, double v1, unsigned long long* s2, double v2,
+                          unsigned long long* s3, double v3) {
+#ifdef MPCB_EMUL
+    umax_accum(s0, v0); umax_accum(s1, v1); umax_accum(s2, v2); umax_accum(s3, v3);
+#else
+    unsigned long long b0 = (unsigned long long)__double_as_longlong(v0), b1 = (unsigned long long)__double_as_longlong(v1);
+    unsigned long long b2 = (unsigned long long)__double_as_longlong(v2), b3 = (unsigned long long)__double_as_longlong(v3);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        const unsigned long long t0 = __shfl_xor_sync(0xffffffffu, b0, o), t1 = __shfl_xor_sync(0xffffffffu, b1, o);
+        const unsigned long long t2 = __shfl_xor_sync(0xffffffffu, b2, o), t3 = __shfl_xor_sync(0xffffffffu, b3, o);
+        b0 = (t0 > b0) ? t0 : b0; b1 = (t1 > b1) ? t1 : b1; b2 = (t2 > b2) ? t2 : b2; b3 = (t3 > b3) ? t3 : b3;
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMax(s0, b0); atomicMax(s1, b1); atomicMax(s2, b2); atomicMax(s3, b3); }
+#endif
+}
 MPCB_DEV double umax_get(const unsigned long long* slot) {
     double v;
     unsigned long long b = *slot;

@@ -921,8 +921,8 @@ MPCB_DEV void admm_run(MPCB_ADRV_PARAMS(SH)) {
             MPCB_WSTAMP(1)
         });
         MPCB_PROF(2)
-        MPCB_APHASE_NS(b_sbi(c, ts, tid));
-        MPCB_APHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); });
+        MPCB_APHASE_NS({ b_sbi(c, ts, tid); MPCB_ISTAMP(12) });
+        MPCB_APHASE_NS({ ts.acc2 = ts.acc + MPCB_PEER(acc, 1); MPCB_ISTAMP(13) });
         MPCB_APHASE({
             const double s4 = ts.acc2 + MPCB_PEER(acc2, 2);
             if (tid < 4 * (SH::NB - 1) && (tid & 3) == 0) c.rB[tid >> 2] = c.rhs[L::sepidx(tid >> 2)] - s4;

@@ -49,7 +49,7 @@ for s_, nm in enumerate(names2):
     ends = [out[64 + 16 * s_ + w] - t0 for w in range(16)]
     print(f"  {nm:16s} " + " ".join(f"{e:5d}" for e in ends))
 print(f"  {'after E barrier':16s} " + " ".join(f"{out[64 + 16 * 6 + w] - t0:5d}" for w in range(16)))
-inner = {7: "B: vector + chunk 0 arrived", 8: "B: chunk-0 products issued", 9: "B: register products issued", 10: "B: all products issued (before the reduce)", 11: "B: transpose-reduce done"}
+inner = {7: "B: vector + chunk 0 arrived", 8: "B: chunk-0 products issued", 9: "B: register products issued", 10: "B: all products issued (before the reduce)", 11: "B: transpose-reduce done", 12: "B': unit sums formed", 13: "B': first pair exchange done"}
 if any(out[64 + 16 * k_ + w] for k_ in inner for w in range(16)):
     print("time stamps inside phase B (same origin):")
     for k_, nm in inner.items():

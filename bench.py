@@ -34,10 +34,10 @@ METRIC = "solved OCPs/sec (mpc_benchmark shape)"
 UNIT = "OCP/s"
 GUESS = "jerk-limited synchronised profile (csrc/mpcb_otg.h, Ruckig's role; pinned on the reference-embedded Ruckig trajectory)"
 # DRAM bytes of one admm_kernel launch per OCP, from the committed ncu --set full capture of the kernel on the base shape
-# (tools/gpu_round2.sh: dram__bytes_read.sum 64.78 MB + dram__bytes_write.sum 0.74 MB for a 148-OCP launch): the factorised QP block
+# (tools/gpu_round2.sh: dram__bytes_read.sum 64.78 MB + dram__bytes_write.sum 0.72 MB for a 148-OCP launch): the factorised QP block
 # of every OCP is read once per QP.
-NCU_ADMM_DRAM_BYTES_PER_OCP = (64.783616e6 + 0.735744e6) / 148
-NCU_TRAFFIC_SOURCE = "ncu --set full, profiles/r2z_admm_kernel_raw.csv (dram read + write of one 148-OCP admm_kernel launch, scaled to the batch)"
+NCU_ADMM_DRAM_BYTES_PER_OCP = (64.782336e6 + 0.716032e6) / 148
+NCU_TRAFFIC_SOURCE = "ncu --set full, profiles/r2zc_admm_kernel_raw.csv (dram read + write of one 148-OCP admm_kernel launch, scaled to the batch)"
 
 
 def workload_name(po, ns, B):

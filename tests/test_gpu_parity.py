@@ -229,6 +229,41 @@ def test_chunked_batch_matches_small_batches(solver):
         assert np.array_equal(rst["qp_iters"], st["qp_iters"][sl])
 
 
+@pytest.mark.parametrize("parts,shape", [(4, (3, 6)), (2, (3, 6)), (3, (7, 4))])
+def test_internal_stream_split_is_bitwise_identical(solver, parts, shape):
+    """MPCB_PARTS (opt-in): mpcb_solve_batch splits a chunk of at least two waves over internal streams of the handle (own work counters,
+    workspace slices and matrix blocks per part, fork / join with events).  Same results, bit for bit, as the single-stream path, on a
+    batch that spans two chunks (so that parts and chunks both occur), for the base shape and for a generic one; the per-kind kernel
+    times stay defined (union of the launch spans)."""
+    import os
+    n = 4096 + 700 if shape == (3, 6) else 640
+    s = M.default_settings(poly_order=shape[0], num_seg=shape[1])
+    lim = M.default_limits(BENCH_MARGINS)
+    x0, xT = M.generate_problems(lim, 0, 3, n)
+    gx, gu, gT = M.guess_batch(s, lim, x0, xT)
+    ref = M.Solver(s, lim) if shape != (3, 6) else solver
+    ref.set_limits(lim)
+    rx, ru, rT, _, rst = ref.solve(x0, xT, gx, gu, gT)
+    launches_ref = ref.last_kernel_launches(0) + ref.last_kernel_launches(1) + ref.last_kernel_launches(2)
+    old = os.environ.get("MPCB_PARTS")
+    os.environ["MPCB_PARTS"] = str(parts)
+    try:
+        sv = M.Solver(s, lim)
+    finally:
+        if old is None:
+            del os.environ["MPCB_PARTS"]
+        else:
+            os.environ["MPCB_PARTS"] = old
+    sx, su, sT, _, st = sv.solve(x0, xT, gx, gu, gT)
+    assert np.array_equal(sx, rx) and np.array_equal(su, ru) and np.array_equal(sT, rT)
+    for k in ("status", "sqp_iters", "qp_iters_total", "qp_iters", "ls_trials"):
+        assert np.array_equal(st[k], rst[k]), k
+    launches = sv.last_kernel_launches(0) + sv.last_kernel_launches(1) + sv.last_kernel_launches(2)
+    assert launches > launches_ref                       # the split really happened
+    assert 0 < sv.last_kernel_ms(1) <= sv.last_solve_ms() + 1e-3
+    sv.close()
+
+
 def test_large_batch_properties(solver):
     """mpc_benchmark size (1000): every problem terminates with a finite solution that honours the pinned initial state,
     the final-state box up to the solver's own reported violation, and the p bounds."""
